@@ -1,0 +1,8 @@
+"""openflash_b200 — B200-native (sm_100a) implementation of OpenFLASH's MEEM hot path.
+
+Keeps the reference's Geometry / MEEMProblem / MEEMEngine API (package/src/openflash/__init__.py);
+the numerics run in hand-written CUDA kernels behind the C ABI of include/meemb200.h.
+"""
+from .multi_constants import g, rho  # noqa: F401
+from .batch import (BatchPlan, FlatGeometry, solve_batch, device_roots, device_bessel, fp64_peak,  # noqa: F401
+                    ALGO_SCHUR, ALGO_DENSE, ROOTS_REFERENCE, ROOTS_CONVERGED, FREQ_OMEGA, FREQ_M0)

@@ -1,0 +1,316 @@
+"""Batched (geometry x frequency x radiating mode) MEEM solves on one B200.
+
+Host-side half of the C ABI in include/meemb200.h: flattens geometries the way the reference does
+at its engine boundary (meem_engine.py:110-116), owns the device buffers (torch tensors used purely
+as memory) and enqueues the CUDA pipeline.  All arithmetic happens in libmeemb200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import ALGO_DENSE, ALGO_SCHUR, FREQ_M0, FREQ_OMEGA, ROOTS_CONVERGED, ROOTS_REFERENCE  # noqa: F401
+from .multi_constants import rho as RHO_DEFAULT
+
+
+@dataclass
+class FlatGeometry:
+    """One concentric-cylinder geometry as flat arrays.
+
+    ``a`` and ``d`` list the M interior regions (the exterior's ``a=inf, d=0`` are appended when
+    packing, as the reference does); ``NMK`` has M+1 entries; ``mode_flags[r][i]`` tells whether
+    region i moves in radiating mode r (body -> region expansion of meem_engine.py:350-367).
+    """
+    h: float
+    a: Sequence[float]
+    d: Sequence[float]
+    NMK: Sequence[int]
+    mode_flags: Sequence[Sequence[int]] = field(default_factory=list)
+
+    def __post_init__(self):
+        self.a = np.asarray(self.a, dtype=np.float64).ravel()
+        self.d = np.asarray(self.d, dtype=np.float64).ravel()
+        self.NMK = np.asarray(self.NMK, dtype=np.int32).ravel()
+        M = len(self.a)
+        if len(self.d) != M or len(self.NMK) != M + 1:
+            raise ValueError("need len(a) == len(d) == len(NMK) - 1")
+        if len(self.mode_flags) == 0:
+            self.mode_flags = [[1] * M]
+        self.mode_flags = np.asarray(self.mode_flags, dtype=np.uint8).reshape(-1, M)
+
+    @property
+    def M(self):
+        return len(self.a)
+
+    @property
+    def R(self):
+        return self.mode_flags.shape[0]
+
+    @property
+    def size(self):
+        N = self.NMK
+        return int(N[0] + N[-1] + 2 * N[1:-1].sum())
+
+    @classmethod
+    def from_body_map(cls, h, a, d, NMK, body_map, modes=None):
+        """Modes are heaving-body indices (meem_problem.py:37-49); body b moves all its regions."""
+        body_map = np.asarray(body_map)
+        if modes is None:
+            modes = sorted(set(int(b) for b in body_map))
+        flags = [[1 if body_map[i] == b else 0 for i in range(len(body_map))] for b in modes]
+        return cls(h, a, d, NMK, flags)
+
+
+_contexts = {}
+
+
+def get_context(device: int = 0):
+    """One meemb200 context per (process, GPU)."""
+    if device not in _contexts:
+        lib = _lib.load()
+        ctx = C.c_void_p()
+        _lib.check(lib.meemb200_create(int(device), C.byref(ctx)))
+        _contexts[device] = ctx
+    return _contexts[device]
+
+
+class BatchPlan:
+    """A validated, packed batch plus its device buffers; ``solve()`` may be called repeatedly."""
+
+    def __init__(self, geometries: Sequence[FlatGeometry], freqs, *, freq_kind=FREQ_OMEGA, algo=ALGO_SCHUR,
+                 root_mode=ROOTS_REFERENCE, want_x=False, rho: Optional[float] = None, device: int = 0):
+        import torch
+        self.torch = torch
+        self.lib = _lib.load()
+        self.device_index = int(device)
+        self.ctx = get_context(self.device_index)
+        self.device = torch.device("cuda", self.device_index)
+        geometries = list(geometries)
+        if not geometries:
+            raise ValueError("empty batch")
+        self.G = len(geometries)
+        self.freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
+        self.F = len(self.freqs)
+        self.R = np.array([g.R for g in geometries], dtype=np.int32)
+        self.M = np.array([g.M for g in geometries], dtype=np.int32)
+        self.NT = np.array([g.size for g in geometries], dtype=np.int64)
+        self.want_x = bool(want_x)
+        self.algo = int(algo)
+        reg_off = np.zeros(self.G + 1, dtype=np.int32)
+        np.cumsum(self.M + 1, out=reg_off[1:])
+        flag_off = np.zeros(self.G + 1, dtype=np.int64)
+        np.cumsum(self.R.astype(np.int64) * (self.M + 1), out=flag_off[1:])
+        a = np.empty(reg_off[-1], dtype=np.float64)
+        d = np.empty(reg_off[-1], dtype=np.float64)
+        nmk = np.empty(reg_off[-1], dtype=np.int32)
+        flags = np.zeros(flag_off[-1], dtype=np.uint8)
+        h = np.empty(self.G, dtype=np.float64)
+        for gi, g in enumerate(geometries):
+            r0, M = reg_off[gi], g.M
+            a[r0:r0 + M] = g.a
+            a[r0 + M] = np.inf
+            d[r0:r0 + M] = g.d
+            d[r0 + M] = 0.0
+            nmk[r0:r0 + M + 1] = g.NMK
+            h[gi] = g.h
+            fl = np.zeros((g.R, M + 1), dtype=np.uint8)
+            fl[:, :M] = g.mode_flags
+            flags[flag_off[gi]:flag_off[gi + 1]] = fl.ravel()
+        self._keep = (reg_off, h, a, d, nmk, self.R, flag_off, flags)
+        b = _lib.MeemBatch()
+        b.n_geom, b.n_freq = self.G, self.F
+        b.reg_off, b.h, b.a, b.d, b.nmk = (x.ctypes.data for x in (reg_off, h, a, d, nmk))
+        b.n_modes, b.flag_off, b.heaving = self.R.ctypes.data, flag_off.ctypes.data, flags.ctypes.data
+        b.freq = self.freqs.ctypes.data
+        b.freq_kind, b.algo, b.root_mode, b.want_x = int(freq_kind), int(algo), int(root_mode), int(self.want_x)
+        b.rho = float(RHO_DEFAULT if rho is None else rho)
+        plan = C.c_void_p()
+        rc = self.lib.meemb200_plan_create(self.ctx, C.byref(b), C.byref(plan))
+        if rc == -1:
+            raise ValueError(self.lib.meemb200_last_error().decode())
+        _lib.check(rc)
+        self.plan = plan
+        self.info = _lib.MeemPlanInfo()
+        _lib.check(self.lib.meemb200_plan_info(self.plan, C.byref(self.info)))
+        Fq = self.F
+        R64 = self.R.astype(np.int64)
+        self.off_rr = np.concatenate([[0], np.cumsum(Fq * R64 * R64)])
+        self.off_r = np.concatenate([[0], np.cumsum(Fq * R64)])
+        self.off_x = np.concatenate([[0], np.cumsum(Fq * R64 * self.NT)]) if self.want_x else None
+        # device buffers (torch tensors as plain memory) and the pinned staging copy of the inputs
+        nb = int(self.info.input_bytes)
+        self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+        self._refresh_host_blob()
+        with torch.cuda.device(self.device):
+            self.d_blob = torch.empty(nb, dtype=torch.uint8, device=self.device)
+            self.d_ws = torch.empty(int(self.info.workspace_bytes), dtype=torch.uint8, device=self.device)
+            f64 = torch.float64
+            self.d_am = torch.empty(int(self.info.n_rr), dtype=f64, device=self.device)
+            self.d_dp = torch.empty(int(self.info.n_rr), dtype=f64, device=self.device)
+            self.d_force = torch.empty(int(self.info.n_r), dtype=f64, device=self.device)
+            self.d_phase = torch.empty(int(self.info.n_r), dtype=f64, device=self.device)
+            self.d_m0 = torch.empty(int(self.info.n_sys), dtype=f64, device=self.device)
+            self.d_status = torch.empty(int(self.info.n_sys), dtype=torch.int32, device=self.device)
+            self.d_x = torch.empty(2 * int(self.info.n_x), dtype=f64, device=self.device) if self.want_x else None
+        self.out = _lib.MeemOutputs(self.d_am.data_ptr(), self.d_dp.data_ptr(), self.d_force.data_ptr(),
+                                    self.d_phase.data_ptr(), self.d_m0.data_ptr(), self.d_status.data_ptr(),
+                                    self.d_x.data_ptr() if self.want_x else None)
+        self._uploaded = False
+
+    def _refresh_host_blob(self):
+        nb = int(self.info.input_bytes)
+        src = (C.c_ubyte * nb).from_address(self.lib.meemb200_plan_blob(self.plan))
+        self.h_blob.numpy()[:] = np.frombuffer(src, dtype=np.uint8)
+
+    def __del__(self):
+        try:
+            if getattr(self, "plan", None):
+                self.lib.meemb200_plan_destroy(self.plan)
+                self.plan = None
+        except Exception:
+            pass
+
+    # -- data movement -------------------------------------------------------------------------
+    @property
+    def h2d_bytes(self):
+        return int(self.info.input_bytes)
+
+    @property
+    def d2h_bytes(self):
+        return int(16 * self.info.n_rr + 16 * self.info.n_r + 12 * self.info.n_sys + 16 * self.info.n_x)
+
+    def set_frequencies(self, freqs):
+        freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
+        if len(freqs) != self.F:
+            raise ValueError("frequency grid length is fixed by the plan")
+        rc = self.lib.meemb200_plan_set_freq(self.plan, freqs.ctypes.data)
+        if rc == -1:
+            raise ValueError(self.lib.meemb200_last_error().decode())
+        _lib.check(rc)
+        self.freqs = freqs
+        self._refresh_host_blob()
+        self._uploaded = False
+
+    def upload(self):
+        """ONE host->device copy of the packed inputs (pinned memory, current stream)."""
+        self.d_blob.copy_(self.h_blob, non_blocking=True)
+        self._uploaded = True
+
+    def solve(self):
+        """Enqueue the kernels on torch's current stream (asynchronous)."""
+        if not self._uploaded:
+            self.upload()
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.meemb200_solve(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(),
+                                           int(self.info.workspace_bytes), C.byref(self.out), C.c_void_p(stream)))
+
+    def stage_ms(self):
+        ms = (C.c_float * 3)()
+        _lib.check(self.lib.meemb200_last_timing(self.plan, ms))
+        return dict(roots=ms[0], geometry=ms[1], frequency=ms[2])
+
+    def download(self):
+        """Device->host read of all outputs; returns flat numpy arrays."""
+        t = self.torch
+        out = dict(added_mass=self.d_am.cpu().numpy(), damping=self.d_dp.cpu().numpy(),
+                   excitation_force=self.d_force.cpu().numpy(), excitation_phase=self.d_phase.cpu().numpy(),
+                   m0=self.d_m0.cpu().numpy().reshape(self.G, self.F),
+                   status=self.d_status.cpu().numpy().reshape(self.G, self.F))
+        if self.want_x:
+            out["X"] = self.d_x.cpu().numpy().view(np.complex128)
+        t.cuda.current_stream(self.device).synchronize()
+        return out
+
+    def run(self):
+        self.upload()
+        self.solve()
+        return self.split(self.download())
+
+    def split(self, flat):
+        """Per-geometry views with the reference's shapes: added_mass[F,R,R] (force on j, motion of i), ..."""
+        res = []
+        F = self.F
+        for g in range(self.G):
+            R = int(self.R[g])
+            r = dict(
+                added_mass=flat["added_mass"][self.off_rr[g]:self.off_rr[g + 1]].reshape(F, R, R),
+                damping=flat["damping"][self.off_rr[g]:self.off_rr[g + 1]].reshape(F, R, R),
+                excitation_force=flat["excitation_force"][self.off_r[g]:self.off_r[g + 1]].reshape(F, R),
+                excitation_phase=flat["excitation_phase"][self.off_r[g]:self.off_r[g + 1]].reshape(F, R),
+                m0=flat["m0"][g], status=flat["status"][g])
+            if self.want_x:
+                r["X"] = flat["X"][self.off_x[g]:self.off_x[g + 1]].reshape(F, R, int(self.NT[g]))
+            res.append(r)
+        return res
+
+    # -- parity / debugging exports ---------------------------------------------------------------
+    def assemble(self, g=0, f=0):
+        """Dense A [NT,NT], b [R,NT], c [R,p] of system (g, f) (MEEMEngine.assemble_A_multi / b / c)."""
+        t = self.torch
+        if not self._uploaded:
+            self.upload()
+        NT, R = int(self.NT[g]), int(self.R[g])
+        p = NT - int(self._keep[4][self._keep[0][g + 1] - 1])
+        A = t.empty(2 * NT * NT, dtype=t.float64, device=self.device)
+        b = t.empty(2 * R * NT, dtype=t.float64, device=self.device)
+        c = t.empty(2 * R * p, dtype=t.float64, device=self.device)
+        stream = t.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.meemb200_assemble(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(),
+                                              int(self.info.workspace_bytes), g, f, A.data_ptr(), b.data_ptr(),
+                                              c.data_ptr(), C.c_void_p(stream)))
+        return (A.cpu().numpy().view(np.complex128).reshape(NT, NT),
+                b.cpu().numpy().view(np.complex128).reshape(R, NT),
+                c.cpu().numpy().view(np.complex128).reshape(R, p))
+
+
+def solve_batch(geometries, freqs, **kw):
+    """Convenience: plan, upload, solve, download; returns one result dict per geometry."""
+    return BatchPlan(geometries, freqs, **kw).run()
+
+
+def device_roots(freq, h, K, *, freq_kind=FREQ_OMEGA, root_mode=ROOTS_REFERENCE, device=0):
+    """m0[n], m_k[n,K], N_k[n,K] on the GPU (wavenumber + _ensure_m_k_and_N_k_arrays)."""
+    import torch
+    lib = _lib.load()
+    ctx = get_context(device)
+    dev = torch.device("cuda", device)
+    freq = np.atleast_1d(np.asarray(freq, dtype=np.float64))
+    hh = np.ascontiguousarray(np.broadcast_to(np.asarray(h, dtype=np.float64), freq.shape))
+    n = len(freq)
+    d_f = torch.from_numpy(np.ascontiguousarray(freq)).to(dev)
+    d_h = torch.from_numpy(hh).to(dev)
+    m0 = torch.empty(n, dtype=torch.float64, device=dev)
+    mk = torch.empty(n * K, dtype=torch.float64, device=dev)
+    nk = torch.empty(n * K, dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    _lib.check(lib.meemb200_roots(ctx, n, int(K), d_f.data_ptr(), d_h.data_ptr(), int(freq_kind), int(root_mode),
+                                  m0.data_ptr(), mk.data_ptr(), nk.data_ptr(), C.c_void_p(stream)))
+    return m0.cpu().numpy(), mk.cpu().numpy().reshape(n, K), nk.cpu().numpy().reshape(n, K)
+
+
+def device_bessel(kind, x, device=0):
+    """kind 0..7 = I0e, I1e, K0e, K1e, J0, Y0, J1, Y1 evaluated by the device kernels."""
+    import torch
+    lib = _lib.load()
+    ctx = get_context(device)
+    dev = torch.device("cuda", device)
+    d_x = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float64))).to(dev)
+    out = torch.empty_like(d_x)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    _lib.check(lib.meemb200_bessel(ctx, int(kind), d_x.numel(), d_x.data_ptr(), out.data_ptr(), C.c_void_p(stream)))
+    return out.cpu().numpy()
+
+
+def fp64_peak(kind=0, device=0):
+    """Measured FP64 throughput in FLOP/s (0 = DFMA loop, 1 = DMMA m8n8k4) — roofline denominator."""
+    import torch
+    lib = _lib.load()
+    ctx = get_context(device)
+    val = C.c_double()
+    stream = torch.cuda.current_stream(torch.device("cuda", device)).cuda_stream
+    _lib.check(lib.meemb200_fp64_peak(ctx, int(kind), C.byref(val), C.c_void_p(stream)))
+    return val.value

@@ -52,7 +52,7 @@ struct Layout {
     int tab[kMaxRegions + 1];      // offset (doubles) of region i's radial table; tab[M] = int_phi[]
 };
 
-MEEM_HD void make_layout(const Geom& g, Layout& L) {
+MEEM_HDX void make_layout(const Geom& g, Layout& L) {
     const int M = g.M;
     L.M = M;
     int c = 0, t = 0;
@@ -77,7 +77,7 @@ MEEM_HD void make_layout(const Geom& g, Layout& L) {
         L.vel_row[bd] = r; L.vel_h[bd] = hgt; r += hgt;
     }
 }
-MEEM_HD int table_doubles(const Layout& L) { return L.tab[L.M] + L.M; }
+MEEM_HDX int table_doubles(const Layout& L) { return L.tab[L.M] + L.M; }
 
 // me.py:35-36 — (n*pi)/(h-d_i), in that order.
 MEEM_HD double lambda_ni(int n, int i, const Geom& g) { return (double)n * kPi / (g.h - g.d[i]); }

@@ -1,0 +1,1113 @@
+// meemb200: CUDA kernels (sm_100a) and C ABI of the batched MEEM hot path.  See include/meemb200.h.
+//
+// Pipeline of one meemb200_solve (all on the caller's stream):
+//   k_m0, k_mk              dispersion roots per (root set = unique (h, K), frequency)
+//   k_tables                radial Bessel tables + c-vector ingredients per geometry
+//   ALGO_SCHUR: k_geom      per geometry: assemble A11 = A[:p,:p] (real, frequency independent),
+//                           Gaussian elimination of [A11 | E | b1_i], reduce to H^T, u_i, w_j, s_ji
+//               k_freq      per (geometry, frequency): I_mk, T = H I_mk, S = D - I_mk^T T (two FP64
+//                           GEMMs), K x K solve with the single complex column carried last,
+//                           coefficients (+ X on request)
+//   ALGO_DENSE: k_dense     per (geometry, frequency): the reference's N_T x N_T complex system,
+//                           assembled in place and solved by blocked partial-pivot LU
+// Persistent CTAs pull work items from an atomic queue (items are cost-sorted by the planner) and
+// own one scratch slot each, so scratch stays L2-resident.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "../../include/meemb200.h"
+#include "meem_forms.cuh"
+#include "meem_lu.cuh"
+
+using namespace meem;
+
+// ------------------------------------------------------------------------------------------------
+// packed input blob (host-built by the planner, uploaded with one copy)
+struct GeomDesc {
+    int32_t M, R, K, N;          // N = harmonics of the last interior region
+    int32_t NT, p;
+    int32_t reg_off;             // into a / d / nmk
+    int32_t root_set;
+    int64_t flag_off;            // into heaving bytes
+    int64_t tab_off;             // doubles, into tables workspace
+    int64_t gs_off;              // doubles, into geometry-stage store
+    int64_t xg_off;              // doubles, into (G, y0) store (want_x) or -1
+    int64_t out_rr, out_r, out_sys, out_x;
+    double h;
+};
+struct RootSet {
+    double h;
+    int32_t K, pad;
+    int64_t off;                 // doubles into roots workspace: m0[F], mk[F][K], Nk[F][K]
+};
+struct BlobHeader {
+    int32_t n_geom, n_freq, n_sets, freq_kind, root_mode, algo, want_x, pad;
+    double rho;
+    int64_t off_geom, off_sets, off_a, off_d, off_nmk, off_flags, off_freq, off_order;
+    // workspace byte offsets
+    int64_t ws_roots, ws_tables, ws_gstore, ws_xstore, ws_slots, ws_counters;
+    int64_t slot_doubles_geom, slot_doubles_freq, slot_doubles_dense;
+};
+
+struct DevView {   // resolved pointers, built on device from blob + workspace
+    const BlobHeader* hdr;
+    const GeomDesc* geom;
+    const RootSet* sets;
+    const double* a;
+    const double* d;
+    const int32_t* nmk;
+    const uint8_t* flags;
+    const double* freq;
+    const int32_t* order;
+    double* roots;
+    double* tables;
+    double* gstore;
+    double* xstore;
+    double* slots;
+    int* counters;
+};
+
+__device__ __forceinline__ DevView make_view(const void* blob, void* ws) {
+    const char* b = static_cast<const char*>(blob);
+    char* w = static_cast<char*>(ws);
+    const BlobHeader* h = reinterpret_cast<const BlobHeader*>(b);
+    DevView v;
+    v.hdr = h;
+    v.geom = reinterpret_cast<const GeomDesc*>(b + h->off_geom);
+    v.sets = reinterpret_cast<const RootSet*>(b + h->off_sets);
+    v.a = reinterpret_cast<const double*>(b + h->off_a);
+    v.d = reinterpret_cast<const double*>(b + h->off_d);
+    v.nmk = reinterpret_cast<const int32_t*>(b + h->off_nmk);
+    v.flags = reinterpret_cast<const uint8_t*>(b + h->off_flags);
+    v.freq = reinterpret_cast<const double*>(b + h->off_freq);
+    v.order = reinterpret_cast<const int32_t*>(b + h->off_order);
+    v.roots = reinterpret_cast<double*>(w + h->ws_roots);
+    v.tables = reinterpret_cast<double*>(w + h->ws_tables);
+    v.gstore = reinterpret_cast<double*>(w + h->ws_gstore);
+    v.xstore = reinterpret_cast<double*>(w + h->ws_xstore);
+    v.slots = reinterpret_cast<double*>(w + h->ws_slots);
+    v.counters = reinterpret_cast<int*>(w + h->ws_counters);
+    return v;
+}
+
+__device__ __forceinline__ Geom geom_of(const DevView& v, const GeomDesc& gd) {
+    Geom g;
+    g.M = gd.M; g.h = gd.h;
+    g.a = v.a + gd.reg_off; g.d = v.d + gd.reg_off; g.nmk = v.nmk + gd.reg_off;
+    return g;
+}
+
+// geometry-stage store layout (doubles): HT[N*N] | w[R*N] | u[R*N] | s0[R*R] | phi[R] | bc[R] | status
+__host__ __device__ inline int64_t gs_doubles(int N, int R) { return (int64_t)N * N + 2LL * R * N + (int64_t)R * R + 2 * R + 2; }
+
+struct OutPtrs {
+    double *am, *dp, *force, *phase, *m0;
+    int32_t* status;
+    double* x;
+};
+
+// ------------------------------------------------------------------------------------------------
+// roots
+__global__ void k_m0(const void* blob, void* ws) {
+    DevView v = make_view(blob, ws);
+    const int F = v.hdr->n_freq;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= v.hdr->n_sets * F) return;
+    const int s = t / F, f = t - s * F;
+    const RootSet rs = v.sets[s];
+    const double fr = v.freq[f];
+    const double m0 = (v.hdr->freq_kind == MEEMB200_FREQ_M0) ? fr : wavenumber_mode(fr, rs.h, v.hdr->root_mode);
+    v.roots[rs.off + f] = m0;
+}
+
+__global__ void k_mk(const void* blob, void* ws) {
+    DevView v = make_view(blob, ws);
+    const int F = v.hdr->n_freq;
+    const int s = blockIdx.y;
+    const RootSet rs = v.sets[s];
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= F * rs.K) return;
+    const int f = t / rs.K, k = t - f * rs.K;
+    const double m0 = v.roots[rs.off + f];
+    const double mk = mk_entry(k, m0, rs.h, v.hdr->root_mode);
+    double* mkp = v.roots + rs.off + F;
+    double* nkp = mkp + (int64_t)F * rs.K;
+    mkp[(int64_t)f * rs.K + k] = mk;
+    nkp[(int64_t)f * rs.K + k] = nk_entry(k, m0, rs.h, mk);
+}
+
+__global__ void k_roots_flat(int n, int K, const double* freq, const double* h, int freq_kind, int root_mode,
+                             double* m0o, double* mko, double* nko) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * K) return;
+    const int i = t / K, k = t - i * K;
+    const double m0 = (freq_kind == MEEMB200_FREQ_M0) ? freq[i] : wavenumber_mode(freq[i], h[i], root_mode);
+    if (k == 0) m0o[i] = m0;
+    const double mk = mk_entry(k, m0, h[i], root_mode);
+    mko[(int64_t)i * K + k] = mk;
+    nko[(int64_t)i * K + k] = nk_entry(k, m0, h[i], mk);
+}
+
+__global__ void k_bessel(int kind, int64_t n, const double* x, double* out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double j0, y0, j1, y1;
+    switch (kind) {
+        case 0: out[i] = i0e(x[i]); break;
+        case 1: out[i] = i1e(x[i]); break;
+        case 2: out[i] = k0e(x[i]); break;
+        case 3: out[i] = k1e(x[i]); break;
+        default:
+            bessel_jy01(x[i], &j0, &y0, &j1, &y1);
+            out[i] = kind == 4 ? j0 : kind == 5 ? y0 : kind == 6 ? j1 : y1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-geometry tables
+__global__ void k_tables(const void* blob, void* ws) {
+    DevView v = make_view(blob, ws);
+    __shared__ Layout L;
+    const GeomDesc gd = v.geom[blockIdx.x];
+    const Geom g = geom_of(v, gd);
+    if (threadIdx.x == 0) make_layout(g, L);
+    __syncthreads();
+    fill_tables(g, L, v.tables + gd.tab_off, threadIdx.x, blockDim.x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// shared helpers
+__device__ __forceinline__ int next_item(int* counter, int* sh) {
+    __syncthreads();
+    if (threadIdx.x == 0) *sh = atomicAdd(counter, 1);
+    __syncthreads();
+    return *sh;
+}
+
+template <class T>
+__device__ __forceinline__ void cta_zero(T* p, int64_t n) {
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) p[i] = zero_of(T());
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, geometry stage
+template <int NB>
+__global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int n_slots_unused) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ int sh_item, sh_status;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    double* W = v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_geom;
+    for (;;) {
+        const int item = next_item(&v.counters[0], &sh_item);
+        if (item >= v.hdr->n_geom) break;
+        const int gi = v.order[item];
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        if (tid == 0) { make_layout(g, L); sh_status = 0; }
+        __syncthreads();
+        const int p = gd.p, N = gd.N, R = gd.R, M = gd.M;
+        const int ncols = p + N + R;
+        const long ld = ncols;
+        const double* tab = v.tables + gd.tab_off;
+        const uint8_t* flags = v.flags + gd.flag_off;
+        cta_zero(W, (int64_t)p * ld);
+        __syncthreads();
+        fill_A_static<double>(g, L, tab, W, ld, tid, nthr);
+        for (int n = tid; n < N; n += nthr) W[(long)(L.pot_row[M - 1] + n) * ld + p + n] = 1.0;   // E
+        for (int i = 0; i < R; ++i) fill_b_static<double>(g, L, flags + (int64_t)i * (M + 1), W + p + N + i, ld, tid, nthr);
+        __syncthreads();
+        lu_forward<double, NB>(W, ld, p, p, ncols, smem, &sh_status);
+        lu_backward<double, NB>(W, ld, p, p, ncols, smem, p);
+        __syncthreads();
+        // reduce to what the frequency stage needs
+        double* gs = v.gstore + gd.gs_off;
+        double* HT = gs;
+        double* wv = HT + (int64_t)N * N;
+        double* uv = wv + (int64_t)R * N;
+        double* s0 = uv + (int64_t)R * N;
+        double* phi = s0 + R * R;
+        double* bc = phi + R;
+        double* st = bc + R;
+        const int bd = M - 1;
+        const double* TL = tab + L.tab[bd];
+        const int c1L = L.col[bd], c2L = c1L + N;
+        // H[n][n'] = R1'(a)[n] G[c1L+n][n'] + R2'(a)[n] G[c2L+n][n'];  stored transposed
+        for (int e = tid; e < N * N; e += nthr) {
+            const int n = e / N, n2 = e - n * N;
+            double hv = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + n2];
+            if (bd > 0) hv += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + n2];
+            HT[(int64_t)n2 * N + n] = hv;
+        }
+        for (int e = tid; e < R * N; e += nthr) {
+            const int i = e / N, n = e - i * N;
+            double u = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + N + i];
+            if (bd > 0) u += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + N + i];
+            uv[e] = u;
+        }
+        // w_j[n'] = sum_col c_j[col] G[col][n'],  s0[j][i] = sum_col c_j[col] y0_i[col]: one warp per (j, column)
+        for (int t = warp; t < R * (N + R); t += nwarp) {
+            const int j = t / (N + R), cidx = t - j * (N + R);
+            const uint8_t* hvj = flags + (int64_t)j * (M + 1);
+            double acc = 0.0;
+            for (int reg = 0; reg < M; ++reg) {
+                if (!hvj[reg]) continue;
+                const int Nr = g.nmk[reg];
+                const double* T8 = tab + L.tab[reg] + 8 * Nr;
+                for (int n = lane; n < Nr; n += 32) {
+                    acc += T8[n] * W[(long)(L.col[reg] + n) * ld + p + cidx];
+                    if (reg > 0) acc += T8[Nr + n] * W[(long)(L.col[reg] + Nr + n) * ld + p + cidx];
+                }
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) {
+                if (cidx < N) wv[j * N + cidx] = acc;
+                else s0[j * R + (cidx - N)] = acc;
+            }
+        }
+        for (int j = tid; j < R; j += nthr) {
+            phi[j] = phi_sum(g, L, tab, flags + (int64_t)j * (M + 1));
+            bc[j] = b_end_constant(g, flags + (int64_t)j * (M + 1));
+        }
+        if (tid == 0) st[0] = (double)sh_status;
+        if (gd.xg_off >= 0) {     // keep G and y0 for X reconstruction
+            double* xg = v.xstore + gd.xg_off;
+            for (int64_t e = tid; e < (int64_t)p * (N + R); e += nthr) {
+                const int r = (int)(e / (N + R)), c = (int)(e - (int64_t)r * (N + R));
+                xg[e] = W[(long)r * ld + p + c];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// CTA-level FP64 GEMM  C[m][n] = sum_k A[k][m] * B[k][n]  (A stored K-major: "TN"), 256 threads,
+// 64x64 tile, 4x4 register micro-tile, operands staged through shared memory.
+struct GemmSmem {
+    double As[16][64];
+    double Bs[16][64];
+};
+
+template <class Store>
+__device__ void cta_gemm_tn(const double* A, long lda, const double* B, long ldb, int Mm, int Nn, int Kd,
+                            GemmSmem& sm, Store store) {
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    for (int m0 = 0; m0 < Mm; m0 += 64) {
+        for (int n0 = 0; n0 < Nn; n0 += 64) {
+            double acc[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
+            for (int k0 = 0; k0 < Kd; k0 += 16) {
+                __syncthreads();
+                for (int idx = tid; idx < 16 * 64; idx += 256) {
+                    const int kk = idx >> 6, x = idx & 63;
+                    const int k = k0 + kk;
+                    sm.As[kk][x] = (k < Kd && m0 + x < Mm) ? A[(long)k * lda + m0 + x] : 0.0;
+                    sm.Bs[kk][x] = (k < Kd && n0 + x < Nn) ? B[(long)k * ldb + n0 + x] : 0.0;
+                }
+                __syncthreads();
+#pragma unroll
+                for (int kk = 0; kk < 16; ++kk) {
+                    double av[4], bv[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) av[r] = sm.As[kk][ty * 4 + r];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) bv[c] = sm.Bs[kk][tx * 4 + c];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) acc[r][c] = fma(av[r], bv[c], acc[r][c]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int m = m0 + ty * 4 + r, n = n0 + tx * 4 + c;
+                    if (m < Mm && n < Nn) store(m, n, acc[r][c]);
+                }
+        }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, frequency stage: one CTA (256 threads) per (geometry, frequency)
+// slot layout (doubles): Imk[N*K] | T[N*K] | Wf[K*ldf] | ext[2K] | xs[2*R*K] | vv[2*R*N]
+__host__ __device__ inline int freq_ld(int K, int R) { return (K + 1 + 2 * R + 1) & ~1; }
+__host__ __device__ inline int64_t freq_slot_doubles(int N, int K, int R) {
+    return 2LL * N * K + (int64_t)K * freq_ld(K, R) + 2LL * K + 2LL * R * K + 2LL * R * N + 8;
+}
+
+template <int NB>
+__global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, OutPtrs out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    __shared__ int sh_item, sh_status;
+    __shared__ GemmSmem gsm;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int F = v.hdr->n_freq;
+    const int64_t total = (int64_t)v.hdr->n_geom * F;
+    double* slot = v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_freq;
+    for (;;) {
+        const int item = next_item(&v.counters[1], &sh_item);
+        if (item >= total) break;
+        const int gi = v.order[item / F], f = item % F;
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        const RootSet rs = v.sets[gd.root_set];
+        const double m0 = v.roots[rs.off + f];
+        const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+        const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_status = 0; }
+        __syncthreads();
+        const int N = gd.N, K = gd.K, R = gd.R, M = gd.M, p = gd.p;
+        const int ldf = freq_ld(K, R);
+        double* Imk = slot;
+        double* T = Imk + (int64_t)N * K;
+        double* Wf = T + (int64_t)N * K;
+        double* ext = Wf + (int64_t)K * ldf;
+        double* xs = ext + 2 * K;                 // x2_i[k] complex
+        double* vv = xs + 2 * R * K;              // v_i[n] complex
+        const double* gs = v.gstore + gd.gs_off;
+        const double* HT = gs;
+        const double* wv = HT + (int64_t)N * N;
+        const double* uv = wv + (int64_t)R * N;
+        const double* s0 = uv + (int64_t)R * N;
+        const double* phi = s0 + R * R;
+        const double* bc = phi + R;
+        const int gstatus = (int)bc[R];
+        // 1. coupling table and exterior diagonal
+        for (int e = tid; e < N * K; e += nthr) {
+            const int n = e / K, k = e - n * K;
+            Imk[e] = imk(n, k, g, ex, mk, Nk);
+        }
+        for (int k = tid; k < K; k += nthr) {
+            const cplx dg = ext_diag(k, g, ex, mk);
+            ext[2 * k] = dg.re; ext[2 * k + 1] = dg.im;
+        }
+        __syncthreads();
+        // 2. T = H Imk
+        cta_gemm_tn(HT, N, Imk, K, N, K, N, gsm, [&](int m, int n, double val) { T[(long)m * K + n] = val; });
+        // 3. S = D - Imk^T T, column k -> k-1 (k >= 1), the complex column k = 0 -> (K-1 | K)
+        cta_gemm_tn(Imk, K, T, K, K, K, N, gsm, [&](int m, int n, double val) {
+            double sv = -val;
+            if (m == n) sv += ext[2 * n];
+            const int col = (n == 0) ? K - 1 : n - 1;
+            Wf[(long)m * ldf + col] = sv;
+        });
+        for (int k = tid; k < K; k += nthr) Wf[(long)k * ldf + K] = (k == 0) ? ext[1] : 0.0;
+        // right-hand sides  y_i[k] = bc_i Imk[0][k] + sum_n Imk[n][k] u_i[n]
+        for (int e = tid; e < R * K; e += nthr) {
+            const int i = e / K, k = e - i * K;
+            double acc = bc[i] * Imk[k];
+            for (int n = 0; n < N; ++n) acc = fma(Imk[(long)n * K + k], uv[i * N + n], acc);
+            Wf[(long)k * ldf + K + 1 + i] = acc;
+        }
+        __syncthreads();
+        // 4. eliminate the K-1 real columns, then the complex pivot
+        lu_forward<double, NB>(Wf, ldf, K, K - 1, K + 1 + R, smem, &sh_status);
+        __syncthreads();
+        {
+            const double are = Wf[(long)(K - 1) * ldf + K - 1], aim = Wf[(long)(K - 1) * ldf + K];
+            if (tid == 0) {
+                if (are == 0.0 && aim == 0.0) atomicOr(&sh_status, 1);
+                if (!isfinite(are) || !isfinite(aim)) atomicOr(&sh_status, 2);
+            }
+            for (int i = 0; i < R; ++i) {
+                const cplx x0 = cmake(Wf[(long)(K - 1) * ldf + K + 1 + i], 0.0) / cmake(are, aim);
+                if (tid == 0) { xs[2 * (i * K)] = x0.re; xs[2 * (i * K) + 1] = x0.im; }
+                for (int r = tid; r < K - 1; r += nthr) {
+                    const double cre = Wf[(long)r * ldf + K - 1], cim = Wf[(long)r * ldf + K];
+                    const double y = Wf[(long)r * ldf + K + 1 + i];
+                    Wf[(long)r * ldf + K + 1 + i] = y - (x0.re * cre - x0.im * cim);
+                    Wf[(long)r * ldf + K + 1 + R + i] = -(x0.re * cim + x0.im * cre);
+                }
+            }
+        }
+        __syncthreads();
+        lu_backward<double, NB>(Wf, ldf, K - 1, K + 1, K + 1 + 2 * R, smem, K);
+        __syncthreads();
+        for (int e = tid; e < R * (K - 1); e += nthr) {
+            const int i = e / (K - 1), r = e - i * (K - 1);
+            xs[2 * (i * K + r + 1)] = Wf[(long)r * ldf + K + 1 + i];
+            xs[2 * (i * K + r + 1) + 1] = Wf[(long)r * ldf + K + 1 + R + i];
+        }
+        __syncthreads();
+        // 5. v_i = Imk x2_i (complex), one warp per (i, n)
+        for (int t = warp; t < R * N; t += nwarp) {
+            const int i = t / N, n = t - i * N;
+            double ar = 0.0, ai = 0.0;
+            for (int k = lane; k < K; k += 32) {
+                const double c = Imk[(long)n * K + k];
+                ar = fma(c, xs[2 * (i * K + k)], ar);
+                ai = fma(c, xs[2 * (i * K + k) + 1], ai);
+            }
+            ar = warp_sum(ar); ai = warp_sum(ai);
+            if (lane == 0) { vv[2 * t] = ar; vv[2 * t + 1] = ai; }
+        }
+        __syncthreads();
+        // 6. coefficients (eng.py:370-391)
+        const int status = sh_status | gstatus;
+        const int64_t sys = gd.out_sys + f;
+        if (tid == 0) { out.m0[sys] = m0; out.status[sys] = status; }
+        const double hk_angle = ex.inf_m0 ? 0.0 : hankel0_angle(m0 * g.a[M - 1]);
+        for (int t = warp; t < R * R; t += nwarp) {
+            const int j = t / R, i = t - j * R;
+            double ar = 0.0, ai = 0.0;
+            for (int n = lane; n < N; n += 32) {
+                ar = fma(wv[j * N + n], vv[2 * (i * N + n)], ar);
+                ai = fma(wv[j * N + n], vv[2 * (i * N + n) + 1], ai);
+            }
+            ar = warp_sum(ar); ai = warp_sum(ai);
+            if (lane == 0) {
+                const double cre = 2.0 * kPi * ((s0[j * R + i] + ar) + phi[j]);
+                const double cim = 2.0 * kPi * ai;
+                double am = cre * v.hdr->rho;
+                double dpv = ex.inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+                if (status) { am = NAN; dpv = NAN; }
+                const int64_t o = gd.out_rr + ((int64_t)f * R + j) * R + i;
+                out.am[o] = am;
+                out.dp[o] = dpv;
+                if (i == j) {
+                    const int64_t o1 = gd.out_r + (int64_t)f * R + j;
+                    double ph = ex.inf_m0 ? -(kPi / 2.0)
+                                          : -(kPi / 2.0) + atan2(xs[2 * (i * K) + 1], xs[2 * (i * K)]) - hk_angle;
+                    double fo = excitation_force(dpv, m0, g.h, kRhoDefault);
+                    if (status) { ph = NAN; fo = NAN; }
+                    out.force[o1] = fo;
+                    out.phase[o1] = ph;
+                }
+            }
+        }
+        // 7. optional X = [y0 + G v ; x2]
+        if (out.x != nullptr && gd.xg_off >= 0) {
+            const double* xg = v.xstore + gd.xg_off;
+            const int NT = gd.NT;
+            for (int t = warp; t < R * p; t += nwarp) {
+                const int i = t / p, r = t - i * p;
+                const double* grow = xg + (int64_t)r * (N + R);
+                double ar = 0.0, ai = 0.0;
+                for (int n = lane; n < N; n += 32) {
+                    ar = fma(grow[n], vv[2 * (i * N + n)], ar);
+                    ai = fma(grow[n], vv[2 * (i * N + n) + 1], ai);
+                }
+                ar = warp_sum(ar); ai = warp_sum(ai);
+                if (lane == 0) {
+                    double* xo = out.x + 2 * (gd.out_x + ((int64_t)f * R + i) * NT + r);
+                    xo[0] = status ? NAN : grow[N + i] + ar;
+                    xo[1] = status ? NAN : ai;
+                }
+            }
+            for (int e = tid; e < R * K; e += nthr) {
+                const int i = e / K, k = e - i * K;
+                double* xo = out.x + 2 * (gd.out_x + ((int64_t)f * R + i) * NT + p + k);
+                xo[0] = status ? NAN : xs[2 * e];
+                xo[1] = status ? NAN : xs[2 * e + 1];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense path: the reference's N_T x N_T complex system, one CTA (512 threads) per (geometry, frequency)
+template <int NB>
+__global__ void __launch_bounds__(512, 1) k_dense(const void* blob, void* ws, OutPtrs out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    __shared__ int sh_item, sh_status;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int F = v.hdr->n_freq;
+    const int64_t total = (int64_t)v.hdr->n_geom * F;
+    cplx* W = reinterpret_cast<cplx*>(v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_dense);
+    for (;;) {
+        const int item = next_item(&v.counters[1], &sh_item);
+        if (item >= total) break;
+        const int gi = v.order[item / F], f = item % F;
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        const RootSet rs = v.sets[gd.root_set];
+        const double m0 = v.roots[rs.off + f];
+        const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+        const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_status = 0; }
+        __syncthreads();
+        const int K = gd.K, R = gd.R, M = gd.M, p = gd.p, NT = gd.NT;
+        const long ld = NT + R;
+        const double* tab = v.tables + gd.tab_off;
+        const uint8_t* flags = v.flags + gd.flag_off;
+        cta_zero(W, (int64_t)NT * ld);
+        __syncthreads();
+        fill_A_static<cplx>(g, L, tab, W, ld, tid, nthr);
+        fill_A_omega(g, L, tab, ex, mk, Nk, W, ld, tid, nthr);
+        for (int i = 0; i < R; ++i) {
+            const uint8_t* hv = flags + (int64_t)i * (M + 1);
+            fill_b_static<cplx>(g, L, hv, W + NT + i, ld, tid, nthr);
+            const double cst = b_end_constant(g, hv);
+            for (int k = tid; k < K; k += nthr)
+                set_real(W[(long)(L.vel_row[M - 1] + k) * ld + NT + i], cst * imk(0, k, g, ex, mk, Nk));
+        }
+        __syncthreads();
+        lu_forward<cplx, NB>(W, ld, NT, NT, NT + R, smem, &sh_status);
+        lu_backward<cplx, NB>(W, ld, NT, NT, NT + R, smem, NT);
+        __syncthreads();
+        const int status = sh_status;
+        const int64_t sys = gd.out_sys + f;
+        if (tid == 0) { out.m0[sys] = m0; out.status[sys] = status; }
+        const double hk_angle = ex.inf_m0 ? 0.0 : hankel0_angle(m0 * g.a[M - 1]);
+        // coefficients: coef_ji = 2 pi (c_j . X_i[:p] + phi_j)
+        for (int t = warp; t < R * R; t += nwarp) {
+            const int j = t / R, i = t - j * R;
+            const uint8_t* hvj = flags + (int64_t)j * (M + 1);
+            double ar = 0.0, ai = 0.0;
+            for (int reg = 0; reg < M; ++reg) {
+                if (!hvj[reg]) continue;
+                const int Nr = g.nmk[reg];
+                const double* T8 = tab + L.tab[reg] + 8 * Nr;
+                for (int n = lane; n < Nr; n += 32) {
+                    cplx x = W[(long)(L.col[reg] + n) * ld + NT + i];
+                    ar = fma(T8[n], x.re, ar); ai = fma(T8[n], x.im, ai);
+                    if (reg > 0) {
+                        x = W[(long)(L.col[reg] + Nr + n) * ld + NT + i];
+                        ar = fma(T8[Nr + n], x.re, ar); ai = fma(T8[Nr + n], x.im, ai);
+                    }
+                }
+            }
+            ar = warp_sum(ar); ai = warp_sum(ai);
+            if (lane == 0) {
+                const double cre = 2.0 * kPi * (ar + phi_sum(g, L, tab, hvj));
+                const double cim = 2.0 * kPi * ai;
+                double am = cre * v.hdr->rho;
+                double dpv = ex.inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+                if (status) { am = NAN; dpv = NAN; }
+                const int64_t o = gd.out_rr + ((int64_t)f * R + j) * R + i;
+                out.am[o] = am;
+                out.dp[o] = dpv;
+                if (i == j) {
+                    const int64_t o1 = gd.out_r + (int64_t)f * R + j;
+                    const cplx xe = W[(long)p * ld + NT + i];
+                    double ph = ex.inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xe.im, xe.re) - hk_angle;
+                    double fo = excitation_force(dpv, m0, g.h, kRhoDefault);
+                    if (status) { ph = NAN; fo = NAN; }
+                    out.force[o1] = fo;
+                    out.phase[o1] = ph;
+                }
+            }
+        }
+        if (out.x != nullptr) {
+            for (int e = tid; e < R * NT; e += nthr) {
+                const int i = e / NT, r = e - i * NT;
+                const cplx x = W[(long)r * ld + NT + i];
+                double* xo = out.x + 2 * (gd.out_x + ((int64_t)f * R + i) * NT + r);
+                xo[0] = status ? NAN : x.re;
+                xo[1] = status ? NAN : x.im;
+            }
+        }
+    }
+}
+
+// debug export: dense A, b, c of one (geometry, frequency)
+__global__ void k_assemble(const void* blob, void* ws, int gi, int f, cplx* A, cplx* b, cplx* c) {
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int F = v.hdr->n_freq;
+    const GeomDesc gd = v.geom[gi];
+    const Geom g = geom_of(v, gd);
+    const RootSet rs = v.sets[gd.root_set];
+    const double m0 = v.roots[rs.off + f];
+    const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+    const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+    if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); }
+    __syncthreads();
+    const int NT = gd.NT, R = gd.R, M = gd.M, p = gd.p, K = gd.K;
+    const double* tab = v.tables + gd.tab_off;
+    const uint8_t* flags = v.flags + gd.flag_off;
+    if (A) {
+        cta_zero(A, (int64_t)NT * NT);
+        __syncthreads();
+        fill_A_static<cplx>(g, L, tab, A, NT, tid, nthr);
+        fill_A_omega(g, L, tab, ex, mk, Nk, A, NT, tid, nthr);
+    }
+    for (int i = 0; i < R; ++i) {
+        const uint8_t* hv = flags + (int64_t)i * (M + 1);
+        if (b) {
+            cplx* bi = b + (int64_t)i * NT;
+            cta_zero(bi, NT);
+            __syncthreads();
+            fill_b_static<cplx>(g, L, hv, bi, 1, tid, nthr);
+            const double cst = b_end_constant(g, hv);
+            for (int k = tid; k < K; k += nthr) set_real(bi[L.vel_row[M - 1] + k], cst * imk(0, k, g, ex, mk, Nk));
+        }
+        if (c) fill_c<cplx>(g, L, tab, hv, c + (int64_t)i * p, tid, nthr);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// FP64 throughput microbenchmarks (roofline denominator)
+__global__ void k_dfma_peak(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+        a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+__global__ void k_dmma_peak(double* out, int iters) {
+    double a = threadIdx.x * 1e-3, b = 1.0 + threadIdx.x * 1e-6;
+    double c0[2] = {0, 0}, c1[2] = {0, 0}, c2[2] = {0, 0}, c3[2] = {0, 0};
+    for (int i = 0; i < iters; ++i) {
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0[0]), "+d"(c0[1]) : "d"(a), "d"(b));
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c1[0]), "+d"(c1[1]) : "d"(a), "d"(b));
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c2[0]), "+d"(c2[1]) : "d"(a), "d"(b));
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c3[0]), "+d"(c3[1]) : "d"(a), "d"(b));
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = c0[0] + c0[1] + c1[0] + c1[1] + c2[0] + c2[1] + c3[0] + c3[1];
+}
+
+// ================================================================================================
+// host side
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CUDA_TRY(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t e_ = (expr);                                                           \
+        if (e_ != cudaSuccess) return fail(MEEMB200_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct meemb200_ctx {
+    int device;
+    int sm_count;
+    size_t smem_optin;
+};
+
+struct meemb200_plan {
+    meemb200_ctx* ctx;
+    std::vector<unsigned char> blob;
+    BlobHeader* hdr() { return reinterpret_cast<BlobHeader*>(blob.data()); }
+    const BlobHeader* hdr() const { return reinterpret_cast<const BlobHeader*>(blob.data()); }
+    MeemPlanInfo info;
+    std::vector<GeomDesc> geoms;
+    int n_slots_geom, n_slots_work;
+    int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
+    size_t smem_geom, smem_freq, smem_dense;
+    int max_tab_threads;
+    int64_t max_FK;
+    cudaEvent_t ev[4];
+    bool ev_ok;
+};
+
+extern "C" int meemb200_version(void) { return 100; }
+extern "C" const char* meemb200_last_error(void) { return g_err.c_str(); }
+
+extern "C" int meemb200_create(int device, meemb200_ctx** out) {
+    if (!out) return fail(MEEMB200_EINVAL, "ctx pointer is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) return fail(MEEMB200_ENODEV, "no CUDA device: meemb200 has no CPU fallback");
+    if (device < 0 || device >= n) return fail(MEEMB200_EINVAL, "device index out of range");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(MEEMB200_ENODEV, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + ", this library is built for sm_100a only");
+    CUDA_TRY(cudaSetDevice(device));
+    meemb200_ctx* c = new meemb200_ctx;
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->smem_optin = prop.sharedMemPerBlockOptin;
+    *out = c;
+    return MEEMB200_OK;
+}
+extern "C" int meemb200_destroy(meemb200_ctx* c) { delete c; return MEEMB200_OK; }
+extern "C" int meemb200_sm_count(const meemb200_ctx* c) { return c ? c->sm_count : MEEMB200_EINVAL; }
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+template <class T>
+static int pick_nb(int max_rows, size_t limit, size_t reserve) {
+    if (lu_smem_bytes<T, 8>(max_rows) + reserve <= limit) return 8;
+    if (lu_smem_bytes<T, 4>(max_rows) + reserve <= limit) return 4;
+    if (lu_smem_bytes<T, 2>(max_rows) + reserve <= limit) return 2;
+    return 0;
+}
+template <class T>
+static size_t nb_bytes(int nb, int rows) {
+    return nb == 8 ? lu_smem_bytes<T, 8>(rows) : nb == 4 ? lu_smem_bytes<T, 4>(rows) : lu_smem_bytes<T, 2>(rows);
+}
+
+extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb200_plan** out) {
+    if (!ctx || !b || !out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (b->n_geom < 1 || b->n_freq < 1) return fail(MEEMB200_EINVAL, "n_geom and n_freq must be >= 1");
+    if (!b->reg_off || !b->h || !b->a || !b->d || !b->nmk || !b->n_modes || !b->flag_off || !b->heaving || !b->freq)
+        return fail(MEEMB200_EINVAL, "NULL array in MeemBatch");
+    if (b->algo != MEEMB200_ALGO_SCHUR && b->algo != MEEMB200_ALGO_DENSE) return fail(MEEMB200_EINVAL, "unknown algo");
+    if (b->root_mode != MEEMB200_ROOTS_REFERENCE && b->root_mode != MEEMB200_ROOTS_CONVERGED) return fail(MEEMB200_EINVAL, "unknown root_mode");
+    if (b->freq_kind != MEEMB200_FREQ_OMEGA && b->freq_kind != MEEMB200_FREQ_M0) return fail(MEEMB200_EINVAL, "unknown freq_kind");
+    const int G = b->n_geom, F = b->n_freq;
+    for (int f = 0; f < F; ++f) {
+        const double w = b->freq[f];
+        if (!(w > 0.0)) return fail(MEEMB200_EINVAL, "frequencies must be positive (meem_problem.py:31)");
+        if (std::isinf(w) && b->freq_kind == MEEMB200_FREQ_OMEGA) return fail(MEEMB200_EINVAL, "omega must be finite; pass m0=inf with FREQ_M0");
+    }
+    meemb200_plan* P = new meemb200_plan;
+    P->ctx = ctx;
+    P->ev_ok = false;
+    P->geoms.resize(G);
+    std::vector<RootSet> sets;
+    std::vector<double> cost(G);
+    int64_t n_rr = 0, n_r = 0, n_x = 0, tab_tot = 0, gs_tot = 0, xg_tot = 0;
+    int64_t slot_geom = 0, slot_freq = 0, slot_dense = 0;
+    int max_p = 1, max_K = 1, max_NT = 1, max_N = 1;
+    double flops = 0.0;
+    const int64_t total_regs = b->reg_off[G];
+    for (int gi = 0; gi < G; ++gi) {
+        const int r0 = b->reg_off[gi], M = b->reg_off[gi + 1] - r0 - 1;
+        auto bad = [&](const char* m) { delete P; return fail(MEEMB200_EINVAL, std::string("geometry ") + std::to_string(gi) + ": " + m); };
+        if (M < 1 || M > kMaxRegions) return bad("number of interior regions must be in [1, 64]");
+        const double h = b->h[gi];
+        if (!(h > 0.0) || std::isinf(h)) return bad("h must be positive and finite");
+        double prev = 0.0;
+        for (int i = 0; i < M; ++i) {
+            const double ai = b->a[r0 + i], di = b->d[r0 + i];
+            if (!(ai > prev) || std::isinf(ai)) return bad("radii must be positive, finite and strictly increasing (basic_region_geometry.py:29-30)");
+            if (!(di >= 0.0) || !(di < h)) return bad("drafts must satisfy 0 <= d < h");
+            prev = ai;
+        }
+        if (b->d[r0 + M] != 0.0) return bad("the exterior draft d[M] must be 0 (basic_region_geometry.py:154-163)");
+        for (int i = 0; i <= M; ++i)
+            if (b->nmk[r0 + i] < 1) return bad("NMK entries must be >= 1");
+        const int R = b->n_modes[gi];
+        if (R < 1) return bad("n_modes must be >= 1");
+        if (b->flag_off[gi + 1] - b->flag_off[gi] != (int64_t)R * (M + 1)) return bad("heaving flags must hold n_modes*(M+1) bytes");
+        GeomDesc& gd = P->geoms[gi];
+        Geom g{M, h, b->a + r0, b->d + r0, b->nmk + r0};
+        Layout L;
+        make_layout(g, L);
+        gd.M = M; gd.R = R; gd.K = L.K; gd.N = b->nmk[r0 + M - 1];
+        gd.NT = L.NT; gd.p = L.p; gd.reg_off = r0; gd.h = h;
+        gd.flag_off = b->flag_off[gi];
+        int s = -1;
+        for (size_t q = 0; q < sets.size(); ++q)
+            if (sets[q].h == h && sets[q].K == L.K) { s = (int)q; break; }
+        if (s < 0) { RootSet rs; rs.h = h; rs.K = L.K; rs.pad = 0; rs.off = 0; sets.push_back(rs); s = (int)sets.size() - 1; }
+        gd.root_set = s;
+        gd.tab_off = tab_tot; tab_tot += table_doubles(L);
+        gd.gs_off = gs_tot; gs_tot += gs_doubles(gd.N, R);
+        if (b->want_x && b->algo == MEEMB200_ALGO_SCHUR) { gd.xg_off = xg_tot; xg_tot += (int64_t)gd.p * (gd.N + R); }
+        else gd.xg_off = -1;
+        gd.out_rr = n_rr; n_rr += (int64_t)F * R * R;
+        gd.out_r = n_r; n_r += (int64_t)F * R;
+        gd.out_sys = (int64_t)gi * F;
+        gd.out_x = n_x; if (b->want_x) n_x += (int64_t)F * R * gd.NT;
+        slot_geom = std::max<int64_t>(slot_geom, (int64_t)gd.p * (gd.p + gd.N + R));
+        slot_freq = std::max<int64_t>(slot_freq, freq_slot_doubles(gd.N, gd.K, R));
+        slot_dense = std::max<int64_t>(slot_dense, 2LL * gd.NT * (gd.NT + R));
+        max_p = std::max(max_p, gd.p); max_K = std::max(max_K, gd.K); max_NT = std::max(max_NT, gd.NT); max_N = std::max(max_N, gd.N);
+        const double p_ = gd.p, N_ = gd.N, K_ = gd.K, NT_ = gd.NT, R_ = R;
+        if (b->algo == MEEMB200_ALGO_SCHUR) {
+            cost[gi] = 2.0 / 3.0 * p_ * p_ * p_ + 2.0 * p_ * p_ * (N_ + R_);
+            const double per_f = 2.0 * N_ * N_ * K_ + 2.0 * N_ * K_ * K_ + 2.0 / 3.0 * K_ * K_ * K_ + 2.0 * K_ * K_ * (1 + 2 * R_) + 4.0 * N_ * K_ * R_;
+            flops += cost[gi] + per_f * F;
+            cost[gi] += per_f * F;
+        } else {
+            cost[gi] = 8.0 / 3.0 * NT_ * NT_ * NT_ + 8.0 * NT_ * NT_ * R_;
+            flops += cost[gi] * F;
+        }
+    }
+    (void)total_regs;
+    // cost-sorted order (largest first) for the work queues
+    std::vector<int32_t> order(G);
+    for (int i = 0; i < G; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost[x] > cost[y]; });
+    int64_t roots_tot = 0;
+    P->max_FK = 1;
+    for (auto& rs : sets) { rs.off = roots_tot; roots_tot += (int64_t)F * (1 + 2 * rs.K); P->max_FK = std::max<int64_t>(P->max_FK, (int64_t)F * rs.K); }
+    // shared-memory driven panel widths
+    const size_t limit = ctx->smem_optin;
+    P->nb_geom = pick_nb<double>(max_p, limit, 4096);
+    P->nb_freq = pick_nb<double>(max_K, limit / 2 > 100 * 1024 ? limit / 2 - 8192 : limit, 24 * 1024);
+    P->nb_dense = pick_nb<cplx>(max_NT, limit, 4096);
+    if ((b->algo == MEEMB200_ALGO_SCHUR && (!P->nb_geom || !P->nb_freq)) || (b->algo == MEEMB200_ALGO_DENSE && !P->nb_dense)) {
+        delete P;
+        return fail(MEEMB200_EINVAL, "system too large for the shared-memory LU panels");
+    }
+    P->smem_geom = P->nb_geom ? nb_bytes<double>(P->nb_geom, max_p) : 0;
+    P->smem_freq = P->nb_freq ? nb_bytes<double>(P->nb_freq, max_K) : 0;
+    P->smem_dense = P->nb_dense ? nb_bytes<cplx>(P->nb_dense, max_NT) : 0;
+    const int sms = ctx->sm_count;
+    const int64_t n_sys = (int64_t)G * F;
+    P->n_slots_geom = (int)std::min<int64_t>(G, sms);
+    if (b->algo == MEEMB200_ALGO_SCHUR) {
+        const int per_sm = (P->smem_freq + 24 * 1024 <= limit / 2) ? 2 : 1;
+        P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
+    } else {
+        P->n_slots_work = (int)std::min<int64_t>(n_sys, sms);
+    }
+    // blob
+    size_t off = align_up(sizeof(BlobHeader), 16);
+    BlobHeader H;
+    memset(&H, 0, sizeof(H));
+    H.n_geom = G; H.n_freq = F; H.n_sets = (int)sets.size(); H.freq_kind = b->freq_kind; H.root_mode = b->root_mode;
+    H.algo = b->algo; H.want_x = b->want_x ? 1 : 0; H.rho = b->rho;
+    const int64_t nreg = b->reg_off[G];
+    const int64_t nflag = b->flag_off[G];
+    H.off_geom = off; off = align_up(off + sizeof(GeomDesc) * G, 16);
+    H.off_sets = off; off = align_up(off + sizeof(RootSet) * sets.size(), 16);
+    H.off_a = off; off = align_up(off + 8 * nreg, 16);
+    H.off_d = off; off = align_up(off + 8 * nreg, 16);
+    H.off_nmk = off; off = align_up(off + 4 * nreg, 16);
+    H.off_flags = off; off = align_up(off + nflag, 16);
+    H.off_freq = off; off = align_up(off + 8 * (size_t)F, 16);
+    H.off_order = off; off = align_up(off + 4 * (size_t)G, 16);
+    const size_t blob_bytes = off;
+    // workspace
+    size_t w = 0;
+    H.ws_counters = w; w = align_up(w + 64, 256);
+    H.ws_roots = w; w = align_up(w + 8 * (size_t)roots_tot, 256);
+    H.ws_tables = w; w = align_up(w + 8 * (size_t)tab_tot, 256);
+    H.ws_gstore = w; w = align_up(w + 8 * (size_t)gs_tot, 256);
+    H.ws_xstore = w; w = align_up(w + 8 * (size_t)xg_tot, 256);
+    H.slot_doubles_geom = (slot_geom + 31) & ~31LL;
+    H.slot_doubles_freq = (slot_freq + 31) & ~31LL;
+    H.slot_doubles_dense = (slot_dense + 31) & ~31LL;
+    size_t slots_bytes;
+    if (b->algo == MEEMB200_ALGO_SCHUR)
+        slots_bytes = 8 * (size_t)std::max<int64_t>(H.slot_doubles_geom * P->n_slots_geom, H.slot_doubles_freq * P->n_slots_work);
+    else
+        slots_bytes = 8 * (size_t)(H.slot_doubles_dense * P->n_slots_work);
+    H.ws_slots = w; w = align_up(w + slots_bytes, 256);
+    P->blob.assign(blob_bytes, 0);
+    unsigned char* bp = P->blob.data();
+    memcpy(bp, &H, sizeof(H));
+    memcpy(bp + H.off_geom, P->geoms.data(), sizeof(GeomDesc) * G);
+    memcpy(bp + H.off_sets, sets.data(), sizeof(RootSet) * sets.size());
+    memcpy(bp + H.off_a, b->a, 8 * nreg);
+    memcpy(bp + H.off_d, b->d, 8 * nreg);
+    memcpy(bp + H.off_nmk, b->nmk, 4 * nreg);
+    memcpy(bp + H.off_flags, b->heaving, nflag);
+    memcpy(bp + H.off_freq, b->freq, 8 * (size_t)F);
+    memcpy(bp + H.off_order, order.data(), 4 * (size_t)G);
+    // a[M] of each geometry is documented as inf; it is never read
+    P->info.input_bytes = blob_bytes;
+    P->info.workspace_bytes = w;
+    P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
+    P->info.n_launches = (b->algo == MEEMB200_ALGO_SCHUR) ? 5 : 4;
+    P->info.flops = flops;
+    *out = P;
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_plan_destroy(meemb200_plan* p) {
+    if (p && p->ev_ok) for (auto& e : p->ev) cudaEventDestroy(e);
+    delete p;
+    return MEEMB200_OK;
+}
+extern "C" int meemb200_plan_info(const meemb200_plan* p, MeemPlanInfo* info) {
+    if (!p || !info) return fail(MEEMB200_EINVAL, "NULL argument");
+    *info = p->info;
+    return MEEMB200_OK;
+}
+extern "C" const void* meemb200_plan_blob(const meemb200_plan* p) { return p ? p->blob.data() : nullptr; }
+extern "C" int meemb200_plan_offsets(const meemb200_plan* p, int32_t g, int64_t out[6]) {
+    if (!p || !out || g < 0 || g >= (int)p->geoms.size()) return fail(MEEMB200_EINVAL, "bad geometry index");
+    const GeomDesc& gd = p->geoms[g];
+    out[0] = gd.out_rr; out[1] = gd.out_r; out[2] = gd.out_sys; out[3] = gd.out_x; out[4] = gd.NT; out[5] = gd.p;
+    return MEEMB200_OK;
+}
+extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
+    if (!p || !freq) return fail(MEEMB200_EINVAL, "NULL argument");
+    const BlobHeader* h = p->hdr();
+    for (int f = 0; f < h->n_freq; ++f)
+        if (!(freq[f] > 0.0)) return fail(MEEMB200_EINVAL, "frequencies must be positive");
+    memcpy(p->blob.data() + h->off_freq, freq, 8 * (size_t)h->n_freq);
+    return MEEMB200_OK;
+}
+
+template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(k_geom<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
+    if (e != cudaSuccess) return e;
+    k_geom<NB><<<P->n_slots_geom, 512, P->smem_geom, s>>>(in, ws, 0);
+    return cudaGetLastError();
+}
+template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(k_freq<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_freq);
+    if (e != cudaSuccess) return e;
+    k_freq<NB><<<P->n_slots_work, 256, P->smem_freq, s>>>(in, ws, o);
+    return cudaGetLastError();
+}
+template <int NB> static cudaError_t launch_dense(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(k_dense<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_dense);
+    if (e != cudaSuccess) return e;
+    k_dense<NB><<<P->n_slots_work, 512, P->smem_dense, s>>>(in, ws, o);
+    return cudaGetLastError();
+}
+
+static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cudaStream_t s) {
+    const BlobHeader* h = P->hdr();
+    CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 64, s));
+    const int nt = h->n_sets * h->n_freq;
+    k_m0<<<(nt + 127) / 128, 128, 0, s>>>(d_in, d_ws);
+    CUDA_TRY(cudaGetLastError());
+    dim3 grid((unsigned)((P->max_FK + 127) / 128), (unsigned)h->n_sets);
+    k_mk<<<grid, 128, 0, s>>>(d_in, d_ws);
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, const MeemOutputs* out, void* stream) {
+    if (!P || !d_in || !d_ws || !out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
+    if (!out->added_mass || !out->damping || !out->exc_force || !out->exc_phase || !out->m0 || !out->status)
+        return fail(MEEMB200_EINVAL, "NULL output pointer");
+    const BlobHeader* h = P->hdr();
+    if (h->want_x && !out->x) return fail(MEEMB200_EINVAL, "plan was built with want_x but outputs.x is NULL");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!P->ev_ok) {
+        for (auto& e : P->ev) CUDA_TRY(cudaEventCreate(&e));
+        P->ev_ok = true;
+    }
+    OutPtrs o{out->added_mass, out->damping, out->exc_force, out->exc_phase, out->m0, out->status, h->want_x ? out->x : nullptr};
+    CUDA_TRY(cudaEventRecord(P->ev[0], s));
+    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(P->ev[1], s));
+    k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
+    CUDA_TRY(cudaGetLastError());
+    if (h->algo == MEEMB200_ALGO_SCHUR) {
+        CUDA_TRY(P->nb_geom == 8 ? launch_geom<8>(P, d_in, d_ws, s) : P->nb_geom == 4 ? launch_geom<4>(P, d_in, d_ws, s) : launch_geom<2>(P, d_in, d_ws, s));
+        CUDA_TRY(cudaEventRecord(P->ev[2], s));
+        CUDA_TRY(P->nb_freq == 8 ? launch_freq<8>(P, d_in, d_ws, o, s) : P->nb_freq == 4 ? launch_freq<4>(P, d_in, d_ws, o, s) : launch_freq<2>(P, d_in, d_ws, o, s));
+    } else {
+        CUDA_TRY(cudaEventRecord(P->ev[2], s));
+        CUDA_TRY(P->nb_dense == 8 ? launch_dense<8>(P, d_in, d_ws, o, s) : P->nb_dense == 4 ? launch_dense<4>(P, d_in, d_ws, o, s) : launch_dense<2>(P, d_in, d_ws, o, s));
+    }
+    CUDA_TRY(cudaEventRecord(P->ev[3], s));
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[3]) {
+    if (!P || !ms || !P->ev_ok) return fail(MEEMB200_EINVAL, "no solve recorded");
+    for (int i = 0; i < 3; ++i) CUDA_TRY(cudaEventElapsedTime(&ms[i], P->ev[i], P->ev[i + 1]));
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void* stream) {
+    if (!P || !ho) return fail(MEEMB200_EINVAL, "NULL argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const MeemPlanInfo& I = P->info;
+    const size_t b_rr = 8 * (size_t)I.n_rr, b_r = 8 * (size_t)I.n_r, b_m0 = 8 * (size_t)I.n_sys, b_st = 4 * (size_t)I.n_sys, b_x = 16 * (size_t)I.n_x;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off = align_up(off + n, 256); return o; };
+    const size_t o_in = take(I.input_bytes), o_ws = take(I.workspace_bytes), o_am = take(b_rr), o_dp = take(b_rr), o_f = take(b_r),
+                 o_p = take(b_r), o_m0 = take(b_m0), o_st = take(b_st), o_x = take(b_x);
+    char* base = nullptr;
+    CUDA_TRY(cudaMallocAsync(reinterpret_cast<void**>(&base), off, s));
+    MeemOutputs d;
+    d.added_mass = reinterpret_cast<double*>(base + o_am); d.damping = reinterpret_cast<double*>(base + o_dp);
+    d.exc_force = reinterpret_cast<double*>(base + o_f); d.exc_phase = reinterpret_cast<double*>(base + o_p);
+    d.m0 = reinterpret_cast<double*>(base + o_m0); d.status = reinterpret_cast<int32_t*>(base + o_st);
+    d.x = I.n_x ? reinterpret_cast<double*>(base + o_x) : nullptr;
+    cudaError_t e = cudaMemcpyAsync(base + o_in, P->blob.data(), I.input_bytes, cudaMemcpyHostToDevice, s);
+    int rc = MEEMB200_OK;
+    if (e != cudaSuccess) rc = fail(MEEMB200_ECUDA, cudaGetErrorString(e));
+    if (!rc) rc = meemb200_solve(P, base + o_in, base + o_ws, I.workspace_bytes, &d, s);
+    if (!rc) {
+        if (ho->added_mass) cudaMemcpyAsync(ho->added_mass, d.added_mass, b_rr, cudaMemcpyDeviceToHost, s);
+        if (ho->damping) cudaMemcpyAsync(ho->damping, d.damping, b_rr, cudaMemcpyDeviceToHost, s);
+        if (ho->exc_force) cudaMemcpyAsync(ho->exc_force, d.exc_force, b_r, cudaMemcpyDeviceToHost, s);
+        if (ho->exc_phase) cudaMemcpyAsync(ho->exc_phase, d.exc_phase, b_r, cudaMemcpyDeviceToHost, s);
+        if (ho->m0) cudaMemcpyAsync(ho->m0, d.m0, b_m0, cudaMemcpyDeviceToHost, s);
+        if (ho->status) cudaMemcpyAsync(ho->status, d.status, b_st, cudaMemcpyDeviceToHost, s);
+        if (ho->x && I.n_x) cudaMemcpyAsync(ho->x, d.x, b_x, cudaMemcpyDeviceToHost, s);
+    }
+    cudaFreeAsync(base, s);
+    e = cudaStreamSynchronize(s);
+    if (!rc && e != cudaSuccess) rc = fail(MEEMB200_ECUDA, std::string("solve_host: ") + cudaGetErrorString(e));
+    return rc;
+}
+
+extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f,
+                                 double* d_A, double* d_b, double* d_c, void* stream) {
+    if (!P || !d_in || !d_ws) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
+    const BlobHeader* h = P->hdr();
+    if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    if (rc) return rc;
+    k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
+    CUDA_TRY(cudaGetLastError());
+    k_assemble<<<1, 512, 0, s>>>(d_in, d_ws, g, f, reinterpret_cast<cplx*>(d_A), reinterpret_cast<cplx*>(d_b), reinterpret_cast<cplx*>(d_c));
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_roots(meemb200_ctx* ctx, int32_t n, int32_t K, const double* d_freq, const double* d_h, int32_t freq_kind,
+                              int32_t root_mode, double* d_m0, double* d_mk, double* d_Nk, void* stream) {
+    if (!ctx || n < 1 || K < 1 || !d_freq || !d_h || !d_m0 || !d_mk || !d_Nk) return fail(MEEMB200_EINVAL, "bad argument");
+    const int64_t t = (int64_t)n * K;
+    k_roots_flat<<<(unsigned)((t + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(n, K, d_freq, d_h, freq_kind, root_mode, d_m0, d_mk, d_Nk);
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_bessel(meemb200_ctx* ctx, int32_t kind, int64_t n, const double* d_x, double* d_out, void* stream) {
+    if (!ctx || kind < 0 || kind > 7 || n < 1 || !d_x || !d_out) return fail(MEEMB200_EINVAL, "bad argument");
+    k_bessel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(kind, n, d_x, d_out);
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_fp64_peak(meemb200_ctx* ctx, int32_t kind, double* flops, void* stream) {
+    if (!ctx || !flops) return fail(MEEMB200_EINVAL, "bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int blocks = ctx->sm_count * 8, threads = 256, iters = 1 << 15;
+    double* buf = nullptr;
+    CUDA_TRY(cudaMalloc(&buf, sizeof(double) * blocks * threads));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0, s);
+        if (kind == 0) k_dfma_peak<<<blocks, threads, 0, s>>>(buf, iters);
+        else k_dmma_peak<<<blocks, threads, 0, s>>>(buf, iters);
+        cudaEventRecord(e1, s);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaError_t e = cudaGetLastError();
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(buf);
+    if (e != cudaSuccess) return fail(MEEMB200_ECUDA, cudaGetErrorString(e));
+    const double per_thread = kind == 0 ? 8.0 * 2.0 * iters : 4.0 * (8 * 8 * 4 * 2.0 / 32.0) * iters;
+    *flops = per_thread * blocks * threads / (best * 1e-3);
+    return MEEMB200_OK;
+}

@@ -1,0 +1,232 @@
+// CTA-cooperative blocked Gaussian elimination with partial pivoting (FP64 real or complex).
+//
+// Replaces scipy.linalg.lu_factor / lu_solve / solve (LAPACK zgetrf / zgetrs / zgesv) on the
+// reference's hot path (meem_engine.py:312, :609, :633).  Same algorithm as LAPACK's right-looking
+// getrf: unscaled partial pivoting with the |re|+|im| pivot measure (izamax), first maximum wins.
+// No row equilibration — it destroys these systems.
+//
+// The matrix W is row-major [nrows x ld] in generic memory (shared or L2-resident global) and holds
+// the right-hand sides as extra columns, so the forward substitution is fused into the elimination
+// and L is never stored.  Panels of NB columns are staged column-major in shared memory and
+// factorised by ONE warp (pivot search = warp-shuffle arg-max, no block barrier per column);
+// the trailing matrix is updated by all warps with register-tiled rank-NB updates whose L operand
+// is broadcast from shared memory and whose U operand is staged per column chunk.
+#pragma once
+#include "meem_forms.cuh"
+
+namespace meem {
+
+constexpr int kLuChunk = 512;   // columns of U12 staged per pass
+
+template <class T> struct LuTile;            // register tile of the rank-NB update
+template <> struct LuTile<double> { static constexpr int TR = 8, TC = 4; };
+template <> struct LuTile<cplx>   { static constexpr int TR = 4, TC = 2; };
+
+MEEM_HD double zero_of(double) { return 0.0; }
+MEEM_HD cplx zero_of(cplx) { return cmake(0.0, 0.0); }
+MEEM_HD void fnma(double& acc, double a, double b) { acc = fma(-a, b, acc); }
+MEEM_HD void fnma(cplx& acc, cplx a, cplx b) {
+    acc.re = fma(-a.re, b.re, acc.re); acc.re = fma(a.im, b.im, acc.re);
+    acc.im = fma(-a.re, b.im, acc.im); acc.im = fma(-a.im, b.re, acc.im);
+}
+MEEM_HD bool finite_of(double a) { return isfinite(a); }
+MEEM_HD bool finite_of(cplx a) { return isfinite(a.re) && isfinite(a.im); }
+
+template <class T, int NB>
+__host__ __device__ constexpr size_t lu_smem_bytes(int max_rows) {
+    return sizeof(T) * (size_t)NB * ((size_t)max_rows + kLuChunk) + 16 * sizeof(int);
+}
+
+#ifdef __CUDACC__
+
+// W[i][c] -= sum_q Lp[q*lstride + (i - row0)] * Us[q*kLuChunk + (c - c0)]  for i in [r_begin, r_end), c in [c0, c1)
+template <class T, int NB>
+__device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, const T* Lp, int lstride,
+                               int c0, int c1, const T* Us, int nbj) {
+    constexpr int TR = LuTile<T>::TR, TC = LuTile<T>::TC;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const int nrt = (r_end - r_begin + TR - 1) / TR;
+    const int nct = (c1 - c0 + 32 * TC - 1) / (32 * TC);
+    for (int t = warp; t < nrt * nct; t += nwarp) {
+        const int rt = t / nct, ct = t - rt * nct;
+        const int i0 = r_begin + rt * TR;
+        const int cb = c0 + ct * 32 * TC + lane;
+        T acc[TR][TC];
+#pragma unroll
+        for (int r = 0; r < TR; ++r)
+#pragma unroll
+            for (int c = 0; c < TC; ++c) acc[r][c] = zero_of(T());
+        for (int q = 0; q < nbj; ++q) {
+            T l[TR], u[TC];
+#pragma unroll
+            for (int r = 0; r < TR; ++r) l[r] = (i0 + r < r_end) ? Lp[q * lstride + (i0 + r - row0)] : zero_of(T());
+#pragma unroll
+            for (int c = 0; c < TC; ++c) {
+                const int cc = cb + 32 * c;
+                u[c] = (cc < c1) ? Us[q * kLuChunk + (cc - c0)] : zero_of(T());
+            }
+#pragma unroll
+            for (int r = 0; r < TR; ++r)
+#pragma unroll
+                for (int c = 0; c < TC; ++c) fnma(acc[r][c], l[r], u[c]);
+        }
+#pragma unroll
+        for (int r = 0; r < TR; ++r) {
+            if (i0 + r >= r_end) break;
+#pragma unroll
+            for (int c = 0; c < TC; ++c) {
+                const int cc = cb + 32 * c;
+                if (cc < c1) {
+                    T* p = &W[(long)(i0 + r) * ld + cc];
+                    *p = *p + acc[r][c];
+                }
+            }
+        }
+    }
+}
+
+// Forward elimination over pivot columns [0, npiv) of the nrows x ncols row-major matrix W
+// (nrows >= npiv; columns >= npiv ride along as right-hand sides).  On return rows [0, npiv) hold
+// U and the transformed right-hand sides; rows >= npiv hold the Schur remainder in columns >= npiv.
+// status: bit 0 set on an exactly-zero pivot, bit 1 on a non-finite pivot column.
+// smem: lu_smem_bytes<T,NB>(nrows).  All threads of the CTA must call.
+template <class T, int NB>
+__device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsigned char* smem_raw, int* status) {
+    T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][nrows] column-major
+    T* ust = panel + (size_t)NB * nrows;                     // [NB][kLuChunk]
+    int* piv = reinterpret_cast<int*>(ust + (size_t)NB * kLuChunk);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int k0 = 0; k0 < npiv; k0 += NB) {
+        const int nbj = min(NB, npiv - k0);
+        const int rows = nrows - k0;
+        // stage the panel
+        for (int idx = tid; idx < rows * nbj; idx += nthr) {
+            const int i = idx / nbj, q = idx - i * nbj;
+            panel[q * nrows + i] = W[(long)(k0 + i) * ld + k0 + q];
+        }
+        __syncthreads();
+        if (warp == 0) {
+            for (int j = 0; j < nbj; ++j) {
+                double best = -1.0;
+                int bi = 0x7fffffff;
+                for (int i = j + lane; i < rows; i += 32) {
+                    const double v = cabs1(panel[j * nrows + i]);
+                    if (v > best) { best = v; bi = i; }
+                }
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) {
+                    const double ov = __shfl_down_sync(0xffffffffu, best, off);
+                    const int oi = __shfl_down_sync(0xffffffffu, bi, off);
+                    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+                }
+                best = __shfl_sync(0xffffffffu, best, 0);
+                bi = __shfl_sync(0xffffffffu, bi, 0);
+                if (bi >= rows) bi = j;                       // column of NaNs
+                if (lane == 0) {
+                    piv[j] = k0 + bi;
+                    if (!(best < INFINITY) || best < 0.0) atomicOr(status, 2);
+                    else if (best == 0.0) atomicOr(status, 1);
+                }
+                if (bi != j && lane < nbj) {
+                    const T t = panel[lane * nrows + j];
+                    panel[lane * nrows + j] = panel[lane * nrows + bi];
+                    panel[lane * nrows + bi] = t;
+                }
+                __syncwarp();
+                const T pv = panel[j * nrows + j];
+                for (int i = j + 1 + lane; i < rows; i += 32) {
+                    const T l = panel[j * nrows + i] / pv;
+                    panel[j * nrows + i] = l;
+                    for (int q = j + 1; q < nbj; ++q) fnma(panel[q * nrows + i], l, panel[q * nrows + j]);
+                }
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        // U11 back to W (back-substitution reads it there)
+        for (int idx = tid; idx < nbj * nbj; idx += nthr) {
+            const int i = idx / nbj, q = idx - i * nbj;
+            W[(long)(k0 + i) * ld + k0 + q] = panel[q * nrows + i];
+        }
+        const int cr0 = k0 + nbj;
+        for (int cc0 = cr0; cc0 < ncols; cc0 += kLuChunk) {
+            const int cc1 = min(ncols, cc0 + kLuChunk);
+            // row swaps + U12 = L11^{-1} A12, one column per thread
+            for (int c = cc0 + tid; c < cc1; c += nthr) {
+                T u[NB];
+#pragma unroll
+                for (int j = 0; j < NB; ++j) {
+                    if (j < nbj) {
+                        const int r2 = piv[j];
+                        if (r2 != k0 + j) {
+                            T* p1 = &W[(long)(k0 + j) * ld + c];
+                            T* p2 = &W[(long)r2 * ld + c];
+                            const T t = *p1; *p1 = *p2; *p2 = t;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < NB; ++q) {
+                    if (q < nbj) {
+                        T v = W[(long)(k0 + q) * ld + c];
+#pragma unroll
+                        for (int q2 = 0; q2 < NB; ++q2)
+                            if (q2 < q) fnma(v, panel[q2 * nrows + q], u[q2]);
+                        u[q] = v;
+                        W[(long)(k0 + q) * ld + c] = v;
+                        ust[q * kLuChunk + (c - cc0)] = v;
+                    }
+                }
+            }
+            __syncthreads();
+            lu_rank_update<T, NB>(W, ld, k0 + nbj, nrows, k0, panel, nrows, cc0, cc1, ust, nbj);
+            __syncthreads();
+        }
+    }
+}
+
+// Back-substitution U X = Y for right-hand-side columns [c0, c1) after lu_forward (U = rows/cols
+// [0, npiv)); X overwrites Y.  Blocked bottom-up, reusing the rank-NB update for the rows above.
+template <class T, int NB>
+__device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned char* smem_raw, int max_rows) {
+    T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][max_rows]: U[0:k0+nbj, k0:k0+nbj]
+    T* ust = panel + (size_t)NB * max_rows;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int nblk = (npiv + NB - 1) / NB;
+    for (int blk = nblk - 1; blk >= 0; --blk) {
+        const int k0 = blk * NB;
+        const int nbj = min(NB, npiv - k0);
+        const int rows = k0 + nbj;
+        for (int idx = tid; idx < rows * nbj; idx += nthr) {
+            const int i = idx / nbj, q = idx - i * nbj;
+            panel[q * max_rows + i] = W[(long)i * ld + k0 + q];
+        }
+        __syncthreads();
+        for (int cc0 = c0; cc0 < c1; cc0 += kLuChunk) {
+            const int cc1 = min(c1, cc0 + kLuChunk);
+            for (int c = cc0 + tid; c < cc1; c += nthr) {
+                T x[NB];
+#pragma unroll
+                for (int q = NB - 1; q >= 0; --q) {
+                    if (q < nbj) {
+                        T v = W[(long)(k0 + q) * ld + c];
+#pragma unroll
+                        for (int q2 = NB - 1; q2 >= 0; --q2)
+                            if (q2 > q && q2 < nbj) fnma(v, panel[q2 * max_rows + k0 + q], x[q2]);
+                        v = v / panel[q * max_rows + k0 + q];
+                        x[q] = v;
+                        W[(long)(k0 + q) * ld + c] = v;
+                        ust[q * kLuChunk + (c - cc0)] = v;
+                    }
+                }
+            }
+            __syncthreads();
+            lu_rank_update<T, NB>(W, ld, 0, k0, 0, panel, max_rows, cc0, cc1, ust, nbj);
+            __syncthreads();
+        }
+    }
+}
+
+#endif  // __CUDACC__
+}  // namespace meem

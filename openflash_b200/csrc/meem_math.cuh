@@ -12,9 +12,11 @@
 
 #ifdef __CUDACC__
 #define MEEM_HD __device__ __forceinline__
+#define MEEM_HDX __host__ __device__ inline      // table-free helpers the host-side planner shares
 #define MEEM_CONST_TABLE static __constant__ const
 #else
 #define MEEM_HD static inline
+#define MEEM_HDX static inline
 #define MEEM_CONST_TABLE static const
 #endif
 
@@ -198,7 +200,7 @@ MEEM_HD double mk_ftan(double x, double c) { return x * tan(x) + c; }
 
 MEEM_HD double mk_root_x_ref(int k, double c) {
     const double xtol = 2e-12, rtol = 8.881784197001252e-16;
-    double xpre = nextafter(kPi * (k - 0.5), INFINITY), xcur = nextafter(kPi * k, INFINITY);
+    double xpre = nextafter(kPi * (k - 0.5), HUGE_VAL), xcur = nextafter(kPi * (double)k, HUGE_VAL);
     double xblk = 0.0, fblk = 0.0, spre = 0.0, scur = 0.0;
     double fpre = mk_ftan(xpre, c), fcur = mk_ftan(xcur, c);
     if (fpre == 0.0) return xpre;

@@ -1,0 +1,160 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the committed golden
+fixtures of the untouched reference.  Tolerances follow SURVEY §8c / BASELINE.json: coefficients
+1e-10 relative, phase 1e-10 absolute (mod 2 pi), wavenumbers 5e-12 (roots are replayed, typically 1e-15)."""
+import numpy as np
+import pytest
+
+from oracle import meem_oracle as mo
+from helpers import load_npz, relerr, phase_err
+
+pytestmark = pytest.mark.gpu
+
+Z1, META1 = load_npz("ref_single.npz")
+Z2, META2 = load_npz("ref_sweeps.npz")
+
+
+@pytest.fixture(scope="module")
+def ofb():
+    import openflash_b200 as ofb
+    return ofb
+
+
+def _check(out, ref, tol=1e-10):
+    for var in ("added_mass", "damping", "excitation_force"):
+        r = ref[var]
+        ok = np.isfinite(r)
+        assert np.array_equal(np.isfinite(out[var]), ok), var
+        assert relerr(out[var][ok], r[ok]) <= tol, (var, relerr(out[var][ok], r[ok]))
+    assert phase_err(out["excitation_phase"], ref["excitation_phase"]) <= tol
+
+
+def test_device_bessel_and_roots(ofb):
+    from scipy.special import ive, kve, hankel1
+    rng = np.random.default_rng(3)
+    x = np.exp(rng.uniform(np.log(1e-3), np.log(3000), 20000))
+    assert relerr(ofb.device_bessel(0, x), ive(0, x)) < 3e-15
+    assert relerr(ofb.device_bessel(1, x), ive(1, x)) < 3e-15
+    assert relerr(ofb.device_bessel(2, x), kve(0, x)) < 6e-15
+    assert relerr(ofb.device_bessel(3, x), kve(1, x)) < 3e-15
+    xs = np.exp(rng.uniform(np.log(1e-4), np.log(500), 20000))
+    H0 = ofb.device_bessel(4, xs) + 1j * ofb.device_bessel(5, xs)
+    H1 = ofb.device_bessel(6, xs) + 1j * ofb.device_bessel(7, xs)
+    assert np.max(np.abs(H0 - hankel1(0, xs)) / np.abs(H0)) < 3e-15
+    assert np.max(np.abs(H1 / H0 - hankel1(1, xs) / hankel1(0, xs)) / np.abs(H1 / H0)) < 4e-15
+    for h in (1.001, 20.0, 50.0):
+        om = np.linspace(0.1, 3.0, 64)
+        for mode, tol in ((ofb.ROOTS_REFERENCE, 2e-14), (ofb.ROOTS_CONVERGED, 5e-12)):
+            m0, mk, nk = ofb.device_roots(om, h, 50, root_mode=mode)
+            ref_m0 = np.array([mo.wavenumber(o, h) for o in om])
+            assert relerr(m0, ref_m0) <= tol
+            for i in (0, 17, 63):
+                ref_mk = mo.m_k_array(50, ref_m0[i], h)
+                assert relerr(mk[i], ref_mk) <= tol
+                k = np.arange(1, 50)   # mode indexing: root k in ((k-1/2)pi, k pi]/h
+                assert np.all(mk[i, 1:] * h > (k - 0.5) * np.pi) and np.all(mk[i, 1:] * h <= k * np.pi * (1 + 5e-16))
+                assert relerr(nk[i], mo.N_k_array(ref_m0[i], h, ref_mk)) <= 1e-9
+
+
+@pytest.mark.parametrize("algo", ["schur", "dense"])
+@pytest.mark.parametrize("name", sorted(META1))
+def test_single_solves_vs_reference(ofb, name, algo):
+    """A, b, X and coefficients for the golden (case, heaving body, m0) set, m0 injected."""
+    c = META1[name]
+    nb = max(c["body_map"]) + 1
+    geo = ofb.FlatGeometry.from_body_map(c["h"], c["a"], c["d"], c["NMK"], c["body_map"], list(range(nb)))
+    plan = ofb.BatchPlan([geo], c["m0"], freq_kind=ofb.FREQ_M0, want_x=True,
+                         algo=ofb.ALGO_SCHUR if algo == "schur" else ofb.ALGO_DENSE)
+    res = plan.run()[0]
+    assert np.all(res["status"] == 0)
+    for mi, m0 in enumerate(c["m0"]):
+        if algo == "dense":
+            A, b, cv = plan.assemble(0, mi)
+        for body in range(nb):
+            key = f"{name}/b{body}/m{mi}"
+            if algo == "dense":
+                assert relerr(b[body], Z1[key + "/b"]) <= 1e-12
+                if body == 0 and key + "/A" in Z1:
+                    Aref = Z1[key + "/A"]
+                    assert np.array_equal(A != 0, Aref != 0)
+                    assert relerr(A, Aref) <= 1e-12
+            Xref = Z1[key + "/X"]
+            X = res["X"][mi, body]
+            assert np.max(np.abs(X - Xref)) <= 1e-9 * np.max(np.abs(Xref))
+            # reference dicts: one entry per mode j for the solution of mode `body`
+            assert relerr(res["added_mass"][mi, :, body], Z1[key + "/real"]) <= 1e-10
+            assert relerr(res["damping"][mi, :, body], Z1[key + "/imag"]) <= 1e-10
+            assert phase_err(res["excitation_phase"][mi, body], Z1[key + "/phase"][body]) <= 1e-10
+            f_ref = Z1[key + "/force"][body]
+            if np.isfinite(f_ref):
+                assert relerr(res["excitation_force"][mi, body], f_ref) <= 1e-10
+            else:
+                assert not np.isfinite(res["excitation_force"][mi, body])
+
+
+@pytest.mark.parametrize("algo", ["schur", "dense"])
+@pytest.mark.parametrize("name", sorted(META2))
+def test_sweeps_vs_run_and_store_results(ofb, name, algo):
+    s = META2[name]
+    geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
+    res = ofb.solve_batch([geo], s["omegas"], algo=ofb.ALGO_SCHUR if algo == "schur" else ofb.ALGO_DENSE, want_x=True)[0]
+    assert relerr(res["m0"], Z2[f"{name}/m0"]) <= 2e-14
+    ref = {v: Z2[f"{name}/{v}"] for v in ("added_mass", "damping", "excitation_force", "excitation_phase")}
+    _check(res, ref)
+    pot = Z2[f"{name}/potentials"]
+    NMK = s["NMK"]
+    col = 0
+    for dom in range(len(NMK)):
+        width = NMK[dom] if dom in (0, len(NMK) - 1) else 2 * NMK[dom]
+        refp = pot[:, :, dom, :width]
+        got = res["X"][:, :, col:col + width]
+        assert np.max(np.abs(got - refp)) <= 1e-9 * np.max(np.abs(refp))
+        col += width
+
+
+def test_m0_infinite_limit(ofb):
+    """solve_linear_system_multi(problem, np.inf) (test_high_frequency_convergence.py)."""
+    geo_o = mo.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [12, 12, 12])
+    flags = [1, 1]
+    X = mo.solve_single(geo_o, flags, np.inf)
+    ref = mo.hydro_coefficients(geo_o, X, np.inf, [flags])[0]
+    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_DENSE):
+        geo = ofb.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [12, 12, 12], [flags])
+        res = ofb.solve_batch([geo], [np.inf], freq_kind=ofb.FREQ_M0, algo=algo, want_x=True)[0]
+        assert relerr(res["added_mass"][0, 0, 0], ref["real"]) <= 1e-10
+        assert res["damping"][0, 0, 0] == 0.0
+        assert abs(res["excitation_phase"][0, 0] + np.pi / 2) < 1e-15
+        assert np.max(np.abs(res["X"][0, 0] - X)) <= 1e-9 * np.max(np.abs(X))
+
+
+def test_overflow_gives_nan_and_status(ofb):
+    """Extreme mode counts overflow exp() -> inf in A -> NaN outputs, batch continues (eng.py:611-614)."""
+    bad = ofb.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [400] * 3)
+    good = ofb.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [20] * 3)
+    res = ofb.solve_batch([bad, good], [1.0, 2.0])
+    assert np.all(res[0]["status"] != 0) and not np.isfinite(res[0]["added_mass"]).any()
+    assert np.all(res[1]["status"] == 0) and np.isfinite(res[1]["added_mass"]).all()
+
+
+def test_heterogeneous_batch_vs_oracle(ofb):
+    """Random N-cylinder geometries (SURVEY §8d C4 generator, small): mixed M, overhangs, shared omega grid."""
+    rng = np.random.default_rng(20260101)
+    geos, ogeos = [], []
+    for _ in range(24):
+        M = int(rng.integers(2, 9))
+        h = 50.0
+        a = np.cumsum(rng.uniform(1.0, 4.0, M))
+        while True:
+            d = np.sort(rng.uniform(0.04, 0.6, M) * h)[::-1]
+            if M == 1 or np.min(-np.diff(d)) >= 0.01 * h:
+                break
+        if rng.uniform() < 0.1:
+            d = rng.permutation(d)
+        NMK = [8] * (M + 1)
+        geos.append(ofb.FlatGeometry(h, a, d, NMK))
+        ogeos.append(mo.FlatGeometry(h, a, d, NMK))
+    om = np.linspace(0.3, 2.5, 5)
+    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_DENSE):
+        res = ofb.solve_batch(geos, om, algo=algo)
+        for g, og in zip(res, ogeos):
+            ref = mo.run_sweep(og, om, [0] * og.M, [0])
+            _check(g, ref)
