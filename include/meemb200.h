@@ -132,8 +132,9 @@ int meemb200_solve(meemb200_plan* plan, const void* d_input, void* d_workspace, 
 int meemb200_solve_host(meemb200_plan* plan, const MeemOutputs* host_out, void* stream);
 
 /* Parity / debugging exports mirroring the reference's intermediate API (device pointers).
- * A: [NT][NT] complex128 row-major, b: [R][NT] complex128, c: [R][p] complex128 for geometry g
- * of the plan at frequency index f.  Any of A/b/c may be NULL. */
+ * A: [NT][NT] complex128 row-major, b: [R][NT] complex128, c: [R][p+1] complex128 (the c vector of
+ * mode j followed by sum_i heaving_j[i]*int_phi_p_i) for geometry g of the plan at frequency index f.
+ * Any of A/b/c may be NULL. */
 int meemb200_assemble(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
                       int32_t g, int32_t f, double* d_A, double* d_b, double* d_c, void* stream);
 /* m0[n], mk[n][K], Nk[n][K] for (freq[i], h[i]) pairs; device pointers. */

@@ -4,5 +4,9 @@ Keeps the reference's Geometry / MEEMProblem / MEEMEngine API (package/src/openf
 the numerics run in hand-written CUDA kernels behind the C ABI of include/meemb200.h.
 """
 from .multi_constants import g, rho  # noqa: F401
+from .model import (Body, SteppedBody, CoordinateBody, BodyArrangement, ConcentricBodyGroup, Domain,  # noqa: F401
+                    Geometry, BasicRegionGeometry, MEEMProblem)
+from .results import Results  # noqa: F401
 from .batch import (BatchPlan, FlatGeometry, solve_batch, device_roots, device_bessel, fp64_peak,  # noqa: F401
                     ALGO_SCHUR, ALGO_DENSE, ROOTS_REFERENCE, ROOTS_CONVERGED, FREQ_OMEGA, FREQ_M0)
+from .meem_engine import MEEMEngine, flatten_problem  # noqa: F401

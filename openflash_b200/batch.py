@@ -249,7 +249,7 @@ class BatchPlan:
 
     # -- parity / debugging exports ---------------------------------------------------------------
     def assemble(self, g=0, f=0):
-        """Dense A [NT,NT], b [R,NT], c [R,p] of system (g, f) (MEEMEngine.assemble_A_multi / b / c)."""
+        """Dense A [NT,NT], b [R,NT], c [R,p], phi [R] of system (g, f) (MEEMEngine.assemble_A_multi / b / c)."""
         t = self.torch
         if not self._uploaded:
             self.upload()
@@ -257,14 +257,15 @@ class BatchPlan:
         p = NT - int(self._keep[4][self._keep[0][g + 1] - 1])
         A = t.empty(2 * NT * NT, dtype=t.float64, device=self.device)
         b = t.empty(2 * R * NT, dtype=t.float64, device=self.device)
-        c = t.empty(2 * R * p, dtype=t.float64, device=self.device)
+        c = t.empty(2 * R * (p + 1), dtype=t.float64, device=self.device)
         stream = t.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.lib.meemb200_assemble(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(),
                                               int(self.info.workspace_bytes), g, f, A.data_ptr(), b.data_ptr(),
                                               c.data_ptr(), C.c_void_p(stream)))
+        cc = c.cpu().numpy().view(np.complex128).reshape(R, p + 1)
         return (A.cpu().numpy().view(np.complex128).reshape(NT, NT),
                 b.cpu().numpy().view(np.complex128).reshape(R, NT),
-                c.cpu().numpy().view(np.complex128).reshape(R, p))
+                np.ascontiguousarray(cc[:, :p]), cc[:, p].real.copy())
 
 
 def solve_batch(geometries, freqs, **kw):

@@ -664,7 +664,10 @@ __global__ void k_assemble(const void* blob, void* ws, int gi, int f, cplx* A, c
             const double cst = b_end_constant(g, hv);
             for (int k = tid; k < K; k += nthr) set_real(bi[L.vel_row[M - 1] + k], cst * imk(0, k, g, ex, mk, Nk));
         }
-        if (c) fill_c<cplx>(g, L, tab, hv, c + (int64_t)i * p, tid, nthr);
+        if (c) {   // c_j[0:p] followed by sum_i heaving_j[i] * int_phi_p_i (eng.py:370-376)
+            fill_c<cplx>(g, L, tab, hv, c + (int64_t)i * (p + 1), tid, nthr);
+            if (tid == 0) set_real(c[(int64_t)i * (p + 1) + p], phi_sum(g, L, tab, hv));
+        }
     }
 }
 

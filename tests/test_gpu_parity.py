@@ -68,7 +68,7 @@ def test_single_solves_vs_reference(ofb, name, algo):
     assert np.all(res["status"] == 0)
     for mi, m0 in enumerate(c["m0"]):
         if algo == "dense":
-            A, b, cv = plan.assemble(0, mi)
+            A, b, cv, phi = plan.assemble(0, mi)
         for body in range(nb):
             key = f"{name}/b{body}/m{mi}"
             if algo == "dense":

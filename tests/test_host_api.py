@@ -1,0 +1,118 @@
+"""CPU tests: object-model validation (mirrors the reference's test_geometry / test_basic_region_geometry /
+test_meem_problem error cases), flattening at the engine boundary, and the C-ABI library exports."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import openflash_b200 as ofb
+from openflash_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _geo(**kw):
+    args = dict(a=np.array([0.5, 1.0]), d=np.array([0.5, 0.25]), h=1.001, NMK=[4, 4, 4], body_map=[0, 1], heaving_map=[True, False])
+    args.update(kw)
+    return ofb.BasicRegionGeometry.from_vectors(**args)
+
+
+def test_library_exports_every_declared_symbol():
+    """include/meemb200.h <-> libmeemb200.so (no compute calls: works without a GPU)."""
+    hdr = open(os.path.join(ROOT, "include", "meemb200.h")).read()
+    declared = set(re.findall(r"\b(meemb200_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.EXPORTS)
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.meemb200_version() >= 100
+
+
+def test_no_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = _lib.load()
+    ctx = ctypes.c_void_p()
+    rc = lib.meemb200_create(0, ctypes.byref(ctx))
+    assert rc == -4 and b"no CPU fallback" in lib.meemb200_last_error()
+    with pytest.raises(Exception):
+        ofb.solve_batch([ofb.FlatGeometry(1.0, [0.5], [0.2], [4, 4])], [1.0])
+
+
+def test_geometry_validation_errors():
+    with pytest.raises(ValueError):
+        _geo(a=np.array([1.0, 0.5]))                       # radii must increase
+    with pytest.raises(ValueError):
+        _geo(NMK=[4, 4])                                   # len(NMK) = len(a) + 1
+    with pytest.raises(ValueError):
+        _geo(heaving_map=[True])                           # heaving_map length
+    with pytest.raises(AssertionError):
+        _geo(heaving_map=[True, True])                     # at most one heaving body
+    with pytest.raises(ValueError):
+        _geo(body_map=[0, 2])                              # body 1 has no radii
+    with pytest.raises(ValueError):
+        ofb.ConcentricBodyGroup([ofb.SteppedBody(np.array([1.0]), np.array([0.1]), np.array([0.0]), True),
+                                 ofb.SteppedBody(np.array([2.0]), np.array([0.1]), np.array([0.0]), True)])
+    with pytest.raises(TypeError):
+        ofb.ConcentricBodyGroup([ofb.CoordinateBody(np.array([1.0, 2.0]), np.array([0.1, 0.2]))])
+    with pytest.raises(AssertionError):
+        ofb.SteppedBody(np.array([1.0, 2.0]), np.array([0.1]), np.array([0.0]))
+    with pytest.raises(AssertionError):
+        ofb.Domain(0, 0, 0.0, 1.0, 0.1, 1.0)
+    with pytest.raises(AssertionError):
+        ofb.Domain(0, 3, 1.0, 0.5, 0.1, 1.0)
+
+
+def test_domains_and_problem():
+    geo = _geo()
+    doms = geo.domain_list
+    assert sorted(doms) == [0, 1, 2]
+    assert doms[2].category == "exterior" and np.isinf(doms[2].a) and doms[2].di == 0.0
+    assert doms[1].a_inner == 0.5 and doms[1].h == 1.001 and doms[0].heaving and not doms[1].heaving
+    prob = ofb.MEEMProblem(geo)
+    assert list(prob.modes) == [0]
+    with pytest.raises(AssertionError):
+        prob.set_frequencies(np.array([1.0, -1.0]))
+    with pytest.raises(AssertionError):
+        prob.set_frequencies([1.0])
+    prob.set_frequencies(np.array([0.5, 1.0]))
+    for b in geo.body_arrangement.bodies:       # multi-mode by flipping flags afterwards
+        b.heaving = True
+    assert list(prob.modes) == [0, 1]
+    flat = ofb.flatten_problem(prob, modes=list(prob.modes))
+    assert flat.M == 2 and flat.R == 2 and flat.size == 16
+    assert flat.mode_flags.tolist() == [[1, 0], [0, 1]]
+    assert np.allclose(flat.a, [0.5, 1.0]) and np.allclose(flat.d, [0.5, 0.25]) and flat.h == 1.001
+
+
+def test_flatten_multi_step_body():
+    geo = ofb.BasicRegionGeometry.from_vectors(a=np.array([5.0, 10.0, 15.0]), d=np.array([15.0, 10.0, 5.0]), h=20.0,
+                                               NMK=[5] * 4, body_map=[0, 1, 1], heaving_map=[False, True])
+    prob = ofb.MEEMProblem(geo)
+    flat = ofb.flatten_problem(prob, modes=[1])
+    assert flat.mode_flags.tolist() == [[0, 1, 1]]
+    flat2 = ofb.flatten_problem(prob, from_domain_flags=True)
+    assert flat2.mode_flags.tolist() == [[0, 1, 1]]
+
+
+def test_results_container_shapes():
+    geo = _geo()
+    prob = ofb.MEEMProblem(geo)
+    prob.set_frequencies(np.array([0.5, 1.0, 2.0]))
+    res = ofb.Results(prob)
+    F, R = 3, 1
+    res.store_hydrodynamic_coefficients(prob.frequencies, np.ones((F, R, R)), np.ones((F, R, R)), np.ones((F, R)),
+                                        np.ones((F, R)), np.ones((F, R, 12), dtype=complex))
+    ds = res.dataset
+    assert ds["added_mass"].dims == ("frequency", "mode_i", "mode_j") and ds["added_mass"].values.shape == (F, R, R)
+    assert ds["excitation_phase"].dims == ("frequency", "mode_i")
+    assert ds["c_vector"].values.shape == (F, R, 12)
+    with pytest.raises(ValueError):
+        res.store_hydrodynamic_coefficients(prob.frequencies, np.ones((F, 2, 2)), np.ones((F, 2, 2)))
+    X = np.arange(F * R * 16, dtype=complex).reshape(F, R, 16)
+    res.store_potential_coefficients(X, [4, 4, 4])
+    pr = ds["potentials_real"].values
+    assert pr.shape == (F, R, 3, 8) and np.isnan(pr[0, 0, 0, 4]) and pr[0, 0, 1, 7] == 11.0 and pr[0, 0, 2, 0] == 12.0
