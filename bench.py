@@ -160,7 +160,7 @@ def run_cpu(geoms, omegas, target_systems, pool):
 
 
 def cpu_target(name):
-    return {"big_tricylinder": 32, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64 * 24}[name]
+    return {"big_tricylinder": 32, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64 * 2}[name]
 
 
 # ------------------------------------------------------------------------------------------ main
@@ -170,7 +170,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="big_tricylinder")
-    ap.add_argument("--algo", default="schur", choices=["schur", "dense"])
+    ap.add_argument("--algo", default="schur", choices=["schur", "schur_lu", "dense"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
@@ -217,7 +217,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     flat = [ofb.FlatGeometry.from_body_map(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"]) for g in geoms]
-    plan = ofb.BatchPlan(flat, omegas, algo=ofb.ALGO_SCHUR if args.algo == "schur" else ofb.ALGO_DENSE, device=local_rank)
+    plan = ofb.BatchPlan(flat, omegas, algo={"schur": ofb.ALGO_SCHUR, "schur_lu": ofb.ALGO_SCHUR_LU, "dense": ofb.ALGO_DENSE}[args.algo], device=local_rank)
     n_out = int(2 * plan.info.n_rr + 2 * plan.info.n_r)
     packed = torch.empty(n_out, dtype=torch.float64, device=dev)
     gathered = torch.empty(n_out * world, dtype=torch.float64, device=dev) if world > 1 else None
@@ -279,16 +279,19 @@ def main():
         peak_dmma = ofb.fp64_peak(1, local_rank)
         peak = max(peak_dfma, peak_dmma)
         st = {k: float(np.mean([x[k] for x in stage])) for k in stage[0]}
+        phase_share = {k: round(v, 4) for k, v in plan.phase_profile().items()} if args.algo == "schur" else None
         dom = max(("geometry", "frequency"), key=lambda k: st[k])
         K_, N_ = int(flat[0].NMK[-1]), int(flat[0].NMK[-2])
-        if args.algo == "schur":
-            R_ = flat[0].R
-            per_sys = 2.0 * N_ * N_ * K_ + 2.0 * N_ * K_ * K_ + 2.0 / 3.0 * K_ ** 3 + 2.0 * K_ * K_ * (1 + 2 * R_) + 4.0 * N_ * K_ * R_
-            freq_flops = sum(len(omegas) * (2.0 * g.NMK[-2] ** 2 * g.NMK[-1] + 2.0 * g.NMK[-2] * g.NMK[-1] ** 2 + 2.0 / 3.0 * g.NMK[-1] ** 3
-                                            + 2.0 * g.NMK[-1] ** 2 * (1 + 2 * g.R) + 4.0 * g.NMK[-2] * g.NMK[-1] * g.R) for g in flat)
+        if args.algo != "dense":
+            def per_f(g):   # closed-form flops of the frequency stage actually executed (kernel table)
+                N, K, R = float(g.NMK[-2]), float(g.NMK[-1]), float(g.R)
+                if args.algo == "schur":
+                    return 2 * N * N * K + N * K * K + K ** 3 / 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R
+                return 2 * N * N * K + 2 * N * K * K + 2 / 3 * K ** 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R
+            freq_flops = sum(len(omegas) * per_f(g) for g in flat)
             geom_flops = float(plan.info.flops) - freq_flops
             kflops = freq_flops if dom == "frequency" else geom_flops
-            kname = "k_freq" if dom == "frequency" else "k_geom"
+            kname = ("k_freq_chol" if args.algo == "schur" else "k_freq_lu") if dom == "frequency" else "k_geom"
         else:
             kflops = float(plan.info.flops)
             kname = "k_dense"
@@ -298,7 +301,7 @@ def main():
                     "frac": achieved / peak, "traffic": None,
                     "peak_source": "measured in this run: max(DFMA register loop %.1f, DMMA m8n8k4 %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
                                    % (peak_dfma / 1e12, peak_dmma / 1e12),
-                    "flops_per_launch": kflops, "kernel_ms": st[dom], "stage_ms": st,
+                    "flops_per_launch": kflops, "kernel_ms": st[dom], "stage_ms": st, "phase_share": phase_share,
                     "dense_equivalent_tflops": value * (8.0 / 3.0 * flat[0].size ** 3 + 8.0 * flat[0].size ** 2 * flat[0].R) / 1e12}
         cpu = None
         if not args.no_cpu and world == 1:

@@ -45,6 +45,7 @@ extern "C" {
 /* algorithm */
 #define MEEMB200_ALGO_SCHUR 0  /* per-geometry real LU of A[:p,:p] + per-frequency KxK Schur system (default) */
 #define MEEMB200_ALGO_DENSE 1  /* reference-shaped: assemble N_T x N_T complex A per system, partial-pivot LU */
+#define MEEMB200_ALGO_SCHUR_LU 2 /* as SCHUR but the K x K frequency system by pivoted LU (the fallback of SCHUR's Cholesky) */
 /* root finder */
 #define MEEMB200_ROOTS_REFERENCE 0 /* replay scipy newton / brentq iterations (closest parity) */
 #define MEEMB200_ROOTS_CONVERGED 1 /* safeguarded Newton to machine precision */
@@ -151,6 +152,12 @@ int meemb200_fp64_peak(meemb200_ctx* ctx, int32_t kind, double* flops, void* str
  * events on the launching stream: ms[0] roots, ms[1] geometry stage, ms[2] frequency stage.
  * Only valid after the stream has been synchronised. */
 int meemb200_last_timing(meemb200_plan* plan, float ms[3]);
+
+/* Per-phase SM-cycle totals (summed over CTAs) of the frequency-stage kernel of the most recent
+ * meemb200_solve that used `d_workspace`: [0] coupling table, [1] column dots / right-hand sides,
+ * [2] T = H Imk, [3] Imk^T T, [4] Cholesky, [5] back-substitution, [6] coefficients, [7] X.
+ * Synchronises the stream.  Measurement only. */
+int meemb200_phase_profile(meemb200_plan* plan, const void* d_workspace, double cycles[8], void* stream);
 
 #ifdef __cplusplus
 }

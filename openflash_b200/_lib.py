@@ -12,7 +12,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmeemb200.so")
 
-ALGO_SCHUR, ALGO_DENSE = 0, 1
+ALGO_SCHUR, ALGO_DENSE, ALGO_SCHUR_LU = 0, 1, 2
 ROOTS_REFERENCE, ROOTS_CONVERGED = 0, 1
 FREQ_OMEGA, FREQ_M0 = 0, 1
 
@@ -53,7 +53,7 @@ EXPORTS = [
     "meemb200_version", "meemb200_last_error", "meemb200_create", "meemb200_destroy", "meemb200_sm_count",
     "meemb200_plan_create", "meemb200_plan_destroy", "meemb200_plan_info", "meemb200_plan_blob",
     "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_solve", "meemb200_solve_host",
-    "meemb200_assemble", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing",
+    "meemb200_assemble", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
 ]
 
 
@@ -87,6 +87,7 @@ def load():
     lib.meemb200_bessel.argtypes = [vp, C.c_int32, C.c_int64, vp, vp, vp]
     lib.meemb200_fp64_peak.argtypes = [vp, C.c_int32, C.POINTER(C.c_double), vp]
     lib.meemb200_last_timing.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.meemb200_phase_profile.argtypes = [vp, vp, C.POINTER(C.c_double), vp]
     _lib = lib
     return lib
 

@@ -13,7 +13,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import ALGO_DENSE, ALGO_SCHUR, FREQ_M0, FREQ_OMEGA, ROOTS_CONVERGED, ROOTS_REFERENCE  # noqa: F401
+from ._lib import ALGO_DENSE, ALGO_SCHUR, ALGO_SCHUR_LU, FREQ_M0, FREQ_OMEGA, ROOTS_CONVERGED, ROOTS_REFERENCE  # noqa: F401
 from .multi_constants import rho as RHO_DEFAULT
 
 
@@ -212,6 +212,16 @@ class BatchPlan:
         ms = (C.c_float * 3)()
         _lib.check(self.lib.meemb200_last_timing(self.plan, ms))
         return dict(roots=ms[0], geometry=ms[1], frequency=ms[2])
+
+    PHASES = ("imk", "dots", "gemm_H_Imk", "gemm_ImkT_T", "cholesky", "backsolve", "coefficients", "x")
+
+    def phase_profile(self):
+        """Share of SM cycles per phase of the frequency-stage kernel of the last solve (measurement only)."""
+        cyc = (C.c_double * 8)()
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.meemb200_phase_profile(self.plan, self.d_ws.data_ptr(), cyc, C.c_void_p(stream)))
+        tot = sum(cyc) or 1.0
+        return {k: cyc[i] / tot for i, k in enumerate(self.PHASES)}
 
     def download(self):
         """Device->host read of all outputs; returns flat numpy arrays."""

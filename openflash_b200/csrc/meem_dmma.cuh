@@ -1,0 +1,151 @@
+// CTA-level FP64 building blocks on the DMMA pipe (mma.sync.aligned.m8n8k4.f64) for sm_100a.
+//
+// Blackwell's tcgen05 / TMEM path has no FP64 kind, so the dense FP64 contractions of the MEEM
+// frequency stage run on the legacy tensor pipe: one m8n8k4 DMMA = 256 FMAs per warp instruction,
+// measured on B200 at the same peak as a pure DFMA stream but with 8x fewer issue slots and 1/8 of
+// the operand traffic from shared memory.  Operands are staged with cp.async (LDGSTS) into padded
+// shared-memory tiles whose row stride is 4 (mod 16) doubles, which makes every fragment load
+// (8 rows x 4 columns of doubles per half-warp) bank-conflict free.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace meem {
+
+// D(8x8) += A(8x4, row) * B(4x8, col).  Lane l holds a = A[l/4][l%4], b = B[l%4][l/4],
+// c0/c1 = C[l/4][2*(l%4) + {0,1}].
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// 16-byte async copy global -> shared; src_bytes = 0 zero-fills the destination.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gsrc), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+// ------------------------------------------------------------------------------------------------
+// C[m][n] = sum_k A[k][m] * B[k][n]   ("TN": both operands stored contraction-major, row-major with
+// leading dimensions lda / ldb, which must be even and the base pointers 16-byte aligned).
+// 256 threads = 8 warps as a 2 x 4 grid of 32 x 32 warp tiles -> CTA tile 64 x 128; contraction is
+// consumed in chunks of kGemmKC rows through a 2-stage cp.async pipeline.  Columns of A / B beyond
+// Mm / Nn (up to the even-padded leading dimension) may hold anything finite or not: they only feed
+// output rows / columns that are never stored.  Rows beyond Kd are zero-filled.
+// lower_only: skip 8x8 blocks that lie strictly above the diagonal (m < n for every element).
+// epi(m, n, v0, v1): called once per lane per stored 8x8 block with the two adjacent columns
+// n, n+1 of row m (n is even); bounds (m < Mm, n < Nn, n+1 < Nn) are the callee's to check.
+constexpr int kGemmKC = 16;
+constexpr int kGemmTM = 64, kGemmTN = 128;
+constexpr int kGemmLdA = kGemmTM + 4, kGemmLdB = kGemmTN + 4;
+constexpr int kGemmStageDoubles = kGemmKC * (kGemmLdA + kGemmLdB);
+constexpr size_t kGemmSmemBytes = 2 * kGemmStageDoubles * sizeof(double);
+
+__device__ __forceinline__ void gemm_stage_load(double* st, const double* A, int lda, const double* B, int ldb,
+                                                int m0, int n0, int Mlim, int Nlim, int k0, int Kd) {
+    const int tid = threadIdx.x;
+    double* As = st;
+    double* Bs = st + kGemmKC * kGemmLdA;
+    // A chunk: KC rows x 64 doubles = 32 x 16-byte groups per row
+#pragma unroll
+    for (int it = 0; it < (kGemmKC * kGemmTM / 2) / 256; ++it) {
+        const int idx = tid + it * 256;
+        const int r = idx >> 5, g = idx & 31;
+        const int k = k0 + r, m = m0 + 2 * g;
+        const bool ok = (k < Kd) && (m < Mlim);
+        cp_async16(As + r * kGemmLdA + 2 * g, ok ? (A + (long)k * lda + m) : A, ok ? 16 : 0);
+    }
+#pragma unroll
+    for (int it = 0; it < (kGemmKC * kGemmTN / 2) / 256; ++it) {
+        const int idx = tid + it * 256;
+        const int r = idx >> 6, g = idx & 63;
+        const int k = k0 + r, n = n0 + 2 * g;
+        const bool ok = (k < Kd) && (n < Nlim);
+        cp_async16(Bs + r * kGemmLdB + 2 * g, ok ? (B + (long)k * ldb + n) : B, ok ? 16 : 0);
+    }
+}
+
+template <class Epi>
+__device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const double* __restrict__ B, int ldb,
+                              int Mm, int Nn, int Kd, bool lower_only, double* sm, Epi epi) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wr = warp >> 2, wc = warp & 3;            // 2 x 4 warps
+    const int lr = lane >> 2, lc = lane & 3;
+    const int Mlim = (Mm + 1) & ~1, Nlim = (Nn + 1) & ~1;
+    const int nchunk = (Kd + kGemmKC - 1) / kGemmKC;
+    // even split of the 8-blocks over CTA tiles
+    const int mb = (Mm + 7) >> 3, nb = (Nn + 7) >> 3;
+    const int tm = (mb + 7) / 8, tn = (nb + 15) / 16;     // number of CTA tiles per dimension
+    for (int ti = 0; ti < tm; ++ti) {
+        const int bm0 = (int)((long)ti * mb / tm), bm1 = (int)((long)(ti + 1) * mb / tm);   // block range of this tile (<= 8)
+        for (int tj = 0; tj < tn; ++tj) {
+            const int bn0 = (int)((long)tj * nb / tn), bn1 = (int)((long)(tj + 1) * nb / tn);   // <= 16 blocks
+            if (lower_only && (bm1 * 8 <= bn0 * 8)) continue;                // whole tile above the diagonal
+            const int m0 = bm0 * 8, n0 = bn0 * 8;
+            // warp's blocks inside the tile: rows split in 2, cols in 4 (even split)
+            const int tmb = bm1 - bm0, tnb = bn1 - bn0;
+            const int rb0 = wr * tmb / 2, rb1 = (wr + 1) * tmb / 2;          // <= 4 blocks
+            const int cb0 = wc * tnb / 4, cb1 = (wc + 1) * tnb / 4;          // <= 4 blocks
+            const int nri = rb1 - rb0, nci = cb1 - cb0;
+            unsigned mask = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    bool on = (i < nri) && (j < nci);
+                    if (on && lower_only) on = (m0 + (rb0 + i) * 8 + 7) >= (n0 + (cb0 + j) * 8);
+                    if (on) mask |= 1u << (i * 4 + j);
+                }
+            double acc[4][4][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+            __syncthreads();      // previous users of the stage buffers are done
+            gemm_stage_load(sm, A, lda, B, ldb, m0, n0, Mlim, Nlim, 0, Kd);
+            cp_async_commit();
+            for (int c = 0; c < nchunk; ++c) {
+                double* cur = sm + (c & 1) * kGemmStageDoubles;
+                if (c + 1 < nchunk) {
+                    gemm_stage_load(sm + ((c + 1) & 1) * kGemmStageDoubles, A, lda, B, ldb, m0, n0, Mlim, Nlim,
+                                    (c + 1) * kGemmKC, Kd);
+                    cp_async_commit();
+                    cp_async_wait<1>();
+                } else {
+                    cp_async_wait<0>();
+                }
+                __syncthreads();
+                if (mask) {
+                    const double* As = cur + rb0 * 8 + lr;
+                    const double* Bs = cur + kGemmKC * kGemmLdA + cb0 * 8 + lr;
+#pragma unroll
+                    for (int ks = 0; ks < kGemmKC / 4; ++ks) {
+                        double af[4], bf[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) af[i] = As[(ks * 4 + lc) * kGemmLdA + i * 8];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) bf[j] = Bs[(ks * 4 + lc) * kGemmLdB + j * 8];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (mask & (1u << (i * 4 + j))) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                    }
+                }
+                __syncthreads();
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (mask & (1u << (i * 4 + j)))
+                        epi(m0 + (rb0 + i) * 8 + lr, n0 + (cb0 + j) * 8 + 2 * lc, acc[i][j][0], acc[i][j][1]);
+        }
+    }
+    __syncthreads();
+}
+
+}  // namespace meem

@@ -25,6 +25,7 @@
 #include "../../include/meemb200.h"
 #include "meem_forms.cuh"
 #include "meem_lu.cuh"
+#include "meem_chol.cuh"
 
 using namespace meem;
 
@@ -104,8 +105,12 @@ __device__ __forceinline__ Geom geom_of(const DevView& v, const GeomDesc& gd) {
     return g;
 }
 
-// geometry-stage store layout (doubles): HT[N*N] | w[R*N] | u[R*N] | s0[R*R] | phi[R] | bc[R] | status
-__host__ __device__ inline int64_t gs_doubles(int N, int R) { return (int64_t)N * N + 2LL * R * N + (int64_t)R * R + 2 * R + 2; }
+// geometry-stage store layout (doubles): HT[N][ldn] | w[R*N] | u[R*N] | s0[R*R] | phi[R] | bc[R] | status
+// ldn = N rounded up to 8 so that rows are 64-byte aligned for the cp.async operand staging.
+__host__ __device__ inline int pad8(int n) { return (n + 7) & ~7; }
+__host__ __device__ inline int64_t gs_doubles(int N, int R) {
+    return (((int64_t)N * pad8(N) + 2LL * R * N + (int64_t)R * R + 2 * R + 2) + 7) & ~7LL;
+}
 
 struct OutPtrs {
     double *am, *dp, *force, *phase, *m0;
@@ -238,7 +243,8 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
         // reduce to what the frequency stage needs
         double* gs = v.gstore + gd.gs_off;
         double* HT = gs;
-        double* wv = HT + (int64_t)N * N;
+        const int ldn = pad8(N);
+        double* wv = HT + (int64_t)N * ldn;
         double* uv = wv + (int64_t)R * N;
         double* s0 = uv + (int64_t)R * N;
         double* phi = s0 + R * R;
@@ -252,8 +258,9 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
             const int n = e / N, n2 = e - n * N;
             double hv = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + n2];
             if (bd > 0) hv += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + n2];
-            HT[(int64_t)n2 * N + n] = hv;
+            HT[(int64_t)n2 * ldn + n] = hv;
         }
+        for (int e = tid; e < N * (ldn - N); e += nthr) HT[(int64_t)(e / (ldn - N)) * ldn + N + e % (ldn - N)] = 0.0;
         for (int e = tid; e < R * N; e += nthr) {
             const int i = e / N, n = e - i * N;
             double u = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + N + i];
@@ -357,12 +364,14 @@ __host__ __device__ inline int64_t freq_slot_doubles(int N, int K, int R) {
     return 2LL * N * K + (int64_t)K * freq_ld(K, R) + 2LL * K + 2LL * R * K + 2LL * R * N + 8;
 }
 
+// Pivoted-LU variant.  only_flagged = 1: re-solve just the systems whose Cholesky (k_freq_chol) hit a
+// non-positive pivot (status bit 2); only_flagged = 0: solve everything (plan option).
 template <int NB>
-__global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, OutPtrs out) {
+__global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, OutPtrs out, int only_flagged) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
-    __shared__ int sh_item, sh_status;
+    __shared__ int sh_item, sh_status, sh_scan;
     __shared__ GemmSmem gsm;
     DevView v = make_view(blob, ws);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -370,8 +379,26 @@ __global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, Out
     const int F = v.hdr->n_freq;
     const int64_t total = (int64_t)v.hdr->n_geom * F;
     double* slot = v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_freq;
+    if (tid == 0) sh_scan = blockIdx.x;
+    __syncthreads();
     for (;;) {
-        const int item = next_item(&v.counters[1], &sh_item);
+        int item;
+        if (only_flagged) {      // static striding: every CTA scans its share of the status words
+            if (tid == 0) {
+                int it = sh_scan;
+                for (; it < total; it += gridDim.x) {
+                    const int gi_ = v.order[it / F];
+                    if (out.status[v.geom[gi_].out_sys + it % F] & 4) break;
+                }
+                sh_item = it;
+                sh_scan = it + gridDim.x;
+            }
+            __syncthreads();
+            item = sh_item;
+            __syncthreads();
+        } else {
+            item = next_item(&v.counters[2], &sh_item);
+        }
         if (item >= total) break;
         const int gi = v.order[item / F], f = item % F;
         const GeomDesc gd = v.geom[gi];
@@ -392,7 +419,8 @@ __global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, Out
         double* vv = xs + 2 * R * K;              // v_i[n] complex
         const double* gs = v.gstore + gd.gs_off;
         const double* HT = gs;
-        const double* wv = HT + (int64_t)N * N;
+        const int ldn = pad8(N);
+        const double* wv = HT + (int64_t)N * ldn;
         const double* uv = wv + (int64_t)R * N;
         const double* s0 = uv + (int64_t)R * N;
         const double* phi = s0 + R * R;
@@ -409,7 +437,7 @@ __global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, Out
         }
         __syncthreads();
         // 2. T = H Imk
-        cta_gemm_tn(HT, N, Imk, K, N, K, N, gsm, [&](int m, int n, double val) { T[(long)m * K + n] = val; });
+        cta_gemm_tn(HT, ldn, Imk, K, N, K, N, gsm, [&](int m, int n, double val) { T[(long)m * K + n] = val; });
         // 3. S = D - Imk^T T, column k -> k-1 (k >= 1), the complex column k = 0 -> (K-1 | K)
         cta_gemm_tn(Imk, K, T, K, K, K, N, gsm, [&](int m, int n, double val) {
             double sv = -val;
@@ -527,6 +555,234 @@ __global__ void __launch_bounds__(256, 2) k_freq(const void* blob, void* ws, Out
                 xo[1] = status ? NAN : xs[2 * e + 1];
             }
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, frequency stage (default): one CTA (256 threads) per (geometry, frequency), DMMA GEMMs
+// + Cholesky.  The exterior index k is stored permuted, kp = k - 1 (k >= 1), k = 0 -> kp = K - 1, so
+// that the single complex diagonal entry sits last and the leading K x K real part is what gets
+// factorised (Sherman-Morrison closes the complex entry; all vector arithmetic stays real).
+// slot layout (doubles): Imk[N][ldk] | T[N][ldk] | P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] |
+//                        ext[ldk] | xc[2*R*K] | vv[2*R*N]
+__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) {
+    const int64_t ldk = pad8(K);
+    return 2LL * N * ldk + (int64_t)(K + R + 1) * ldk + (int64_t)(2 * R + 2) * ldk + 2LL * R * K + 2LL * R * N + 16;
+}
+__host__ __device__ inline size_t freq2_smem_bytes(int K, int R) {
+    const size_t a = kGemmSmemBytes, b = chol_smem_bytes(K, R);
+    return a > b ? a : b;
+}
+
+enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, PH_COUNT };
+
+__global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws, OutPtrs out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    __shared__ int sh_item, sh_fail;
+    __shared__ double sh_dots[64];
+    DevView v = make_view(blob, ws);
+    double* sm = reinterpret_cast<double*>(smem);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int F = v.hdr->n_freq;
+    const int64_t total = (int64_t)v.hdr->n_geom * F;
+    double* slot = v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_freq;
+    long long tph[PH_COUNT];
+#pragma unroll
+    for (int i = 0; i < PH_COUNT; ++i) tph[i] = 0;
+    long long tprev = clock64();
+#define PHASE_END(ph) do { __syncthreads(); const long long tn_ = clock64(); tph[ph] += tn_ - tprev; tprev = tn_; } while (0)
+    for (;;) {
+        const int item = next_item(&v.counters[1], &sh_item);
+        if (item >= total) break;
+        const int gi = v.order[item / F], f = item % F;
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        const RootSet rs = v.sets[gd.root_set];
+        const double m0 = v.roots[rs.off + f];
+        const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+        const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_fail = 0; }
+        __syncthreads();
+        const int N = gd.N, K = gd.K, R = gd.R, M = gd.M, p = gd.p;
+        const int ldk = pad8(K), ldn = pad8(N);
+        double* Imk = slot;
+        double* T = Imk + (int64_t)N * ldk;
+        double* P = T + (int64_t)N * ldk;
+        double* qv = P + (int64_t)(K + R + 1) * ldk;
+        double* xs = qv + (int64_t)R * ldk;
+        double* ext = xs + (int64_t)(R + 1) * ldk;
+        double* xc = ext + ldk;                    // x2_i[k] complex, natural k order
+        double* vv = xc + 2 * R * K;               // v_i[n] complex
+        const double* gs = v.gstore + gd.gs_off;
+        const double* HT = gs;
+        const double* wv = HT + (int64_t)N * ldn;
+        const double* uv = wv + (int64_t)R * N;
+        const double* s0 = uv + (int64_t)R * N;
+        const double* phi = s0 + R * R;
+        const double* bc = phi + R;
+        const int gstatus = (int)bc[R];
+        // 1. coupling table (columns permuted) and exterior diagonal
+        for (int e = tid; e < N * K; e += nthr) {
+            const int n = e / K, kp = e - n * K;
+            const int k = (kp == K - 1) ? 0 : kp + 1;
+            Imk[(long)n * ldk + kp] = imk(n, k, g, ex, mk, Nk);
+        }
+        for (int kp = tid; kp < K; kp += nthr) {
+            const int k = (kp == K - 1) ? 0 : kp + 1;
+            const cplx dg = ext_diag(k, g, ex, mk);
+            ext[kp] = dg.re;
+            if (k == 0) sh_dots[63] = dg.im;
+        }
+        PHASE_END(PH_IMK);
+        // 2. column dots: r_i = -(bc_i Imk[0][:] + Imk^T u_i) (augmented rows of P), q_j = Imk^T w_j
+        for (int t = tid; t < 2 * R * K; t += nthr) {
+            const int vi = t / K, kp = t - vi * K;
+            const double* vec = (vi < R) ? (uv + vi * N) : (wv + (vi - R) * N);
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int n = 0;
+            for (; n + 3 < N; n += 4) {
+                a0 = fma(Imk[(long)n * ldk + kp], vec[n], a0);
+                a1 = fma(Imk[(long)(n + 1) * ldk + kp], vec[n + 1], a1);
+                a2 = fma(Imk[(long)(n + 2) * ldk + kp], vec[n + 2], a2);
+                a3 = fma(Imk[(long)(n + 3) * ldk + kp], vec[n + 3], a3);
+            }
+            for (; n < N; ++n) a0 = fma(Imk[(long)n * ldk + kp], vec[n], a0);
+            const double acc = (a0 + a1) + (a2 + a3);
+            if (vi < R) P[(long)(K + vi) * ldk + kp] = -(bc[vi] * Imk[kp] + acc);
+            else qv[(long)(vi - R) * ldk + kp] = acc;
+        }
+        PHASE_END(PH_DOTS);
+        // 3. T = H Imk
+        cta_gemm_dmma(HT, ldn, Imk, ldk, N, K, N, false, sm, [&](int m, int n, double v0, double v1) {
+            if (m < N && n < K) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
+        });
+        PHASE_END(PH_GEMM1);
+        // 4. P = Imk^T T - Re(D), lower triangle
+        cta_gemm_dmma(Imk, ldk, T, ldk, K, K, N, true, sm, [&](int m, int n, double v0, double v1) {
+            if (m < K && n < K) {
+                if (m == n) v0 -= ext[m];
+                if (m == n + 1) v1 -= ext[m];
+                *reinterpret_cast<double2*>(P + (long)m * ldk + n) = make_double2(v0, v1);
+            }
+        });
+        PHASE_END(PH_GEMM2);
+        // 5. P = L L^T; rows K.. become L^{-1} r_i
+        cta_cholesky(P, ldk, K, R, sm, &sh_fail);
+        PHASE_END(PH_CHOL);
+        // 6. back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last
+        for (int t = tid; t < (R + 1) * K; t += nthr) {
+            const int r = t / K, kp = t - r * K;
+            xs[(long)r * ldk + kp] = (r < R) ? P[(long)(K + r) * ldk + kp]
+                                             : (kp == K - 1 ? 1.0 / P[(long)(K - 1) * ldk + K - 1] : 0.0);
+        }
+        cta_chol_backsolve(P, ldk, K, xs, ldk, R + 1, sm);
+        PHASE_END(PH_BACK);
+        // 7. coefficients (eng.py:370-391).  x2_i = w_i + i beta x_e z,  x_e = w_e / (1 - i beta z_e)
+        const double beta = sh_dots[63];
+        const double* zv = xs + (long)R * ldk;
+        for (int t = warp; t < R * R + R; t += nwarp) {     // q_j . w_i  and  q_j . z
+            const double* qa = qv + (long)((t < R * R) ? t / R : t - R * R) * ldk;
+            const double* xb = (t < R * R) ? xs + (long)(t % R) * ldk : zv;
+            double a = 0.0;
+            for (int k = lane; k < K; k += 32) a = fma(qa[k], xb[k], a);
+            a = warp_sum(a);
+            if (lane == 0 && t < 62) sh_dots[t] = a;
+        }
+        __syncthreads();
+        const int fail = sh_fail;
+        const int status = gstatus | (fail ? 4 : 0);
+        const int64_t sys = gd.out_sys + f;
+        if (tid == 0) { out.m0[sys] = m0; out.status[sys] = status; }
+        const double ze = zv[K - 1];
+        const double den = 1.0 + beta * beta * ze * ze;
+        for (int t = tid; t < R * R; t += nthr) {
+            const int j = t / R, i = t - j * R;
+            const double we = xs[(long)i * ldk + K - 1];
+            const double xer = we / den, xei = we * beta * ze / den;      // x_e = we (1 + i beta ze) / den
+            double qw, qz;
+            if (R * R + R <= 62) { qw = sh_dots[t]; qz = sh_dots[R * R + j]; }
+            else {   // many modes: recompute serially (rare)
+                qw = 0.0; qz = 0.0;
+                for (int k = 0; k < K; ++k) {
+                    qw = fma(qv[(long)j * ldk + k], xs[(long)i * ldk + k], qw);
+                    qz = fma(qv[(long)j * ldk + k], zv[k], qz);
+                }
+            }
+            const double cre = 2.0 * kPi * ((s0[j * R + i] + (qw - beta * xei * qz)) + phi[j]);
+            const double cim = 2.0 * kPi * (beta * xer * qz);
+            double am = cre * v.hdr->rho;
+            double dpv = ex.inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+            if (status) { am = NAN; dpv = NAN; }
+            const int64_t o = gd.out_rr + ((int64_t)f * R + j) * R + i;
+            out.am[o] = am;
+            out.dp[o] = dpv;
+            if (i == j) {
+                const int64_t o1 = gd.out_r + (int64_t)f * R + j;
+                double ph = ex.inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xei, xer) - hankel0_angle(m0 * g.a[M - 1]);
+                double fo = excitation_force(dpv, m0, g.h, kRhoDefault);
+                if (status) { ph = NAN; fo = NAN; }
+                out.force[o1] = fo;
+                out.phase[o1] = ph;
+            }
+        }
+        PHASE_END(PH_OUT);
+        // 8. optional X = [y0 + G v ; x2],  v = Imk x2
+        if (out.x != nullptr && gd.xg_off >= 0) {
+            for (int e = tid; e < R * K; e += nthr) {
+                const int i = e / K, kp = e - i * K;
+                const int k = (kp == K - 1) ? 0 : kp + 1;
+                const double we = xs[(long)i * ldk + K - 1];
+                const double xer = we / den, xei = we * beta * ze / den;
+                xc[2 * (i * K + k)] = xs[(long)i * ldk + kp] - beta * xei * zv[kp];
+                xc[2 * (i * K + k) + 1] = beta * xer * zv[kp];
+            }
+            __syncthreads();
+            for (int t = warp; t < R * N; t += nwarp) {
+                const int i = t / N, n = t - i * N;
+                double ar = 0.0, ai = 0.0;
+                for (int kp = lane; kp < K; kp += 32) {
+                    const int k = (kp == K - 1) ? 0 : kp + 1;
+                    const double c = Imk[(long)n * ldk + kp];
+                    ar = fma(c, xc[2 * (i * K + k)], ar);
+                    ai = fma(c, xc[2 * (i * K + k) + 1], ai);
+                }
+                ar = warp_sum(ar); ai = warp_sum(ai);
+                if (lane == 0) { vv[2 * t] = ar; vv[2 * t + 1] = ai; }
+            }
+            __syncthreads();
+            const double* xg = v.xstore + gd.xg_off;
+            const int NT = gd.NT;
+            for (int t = warp; t < R * p; t += nwarp) {
+                const int i = t / p, r = t - i * p;
+                const double* grow = xg + (int64_t)r * (N + R);
+                double ar = 0.0, ai = 0.0;
+                for (int n = lane; n < N; n += 32) {
+                    ar = fma(grow[n], vv[2 * (i * N + n)], ar);
+                    ai = fma(grow[n], vv[2 * (i * N + n) + 1], ai);
+                }
+                ar = warp_sum(ar); ai = warp_sum(ai);
+                if (lane == 0) {
+                    double* xo = out.x + 2 * (gd.out_x + ((int64_t)f * R + i) * NT + r);
+                    xo[0] = status ? NAN : grow[N + i] + ar;
+                    xo[1] = status ? NAN : ai;
+                }
+            }
+            for (int e = tid; e < R * K; e += nthr) {
+                const int i = e / K, k = e - i * K;
+                double* xo = out.x + 2 * (gd.out_x + ((int64_t)f * R + i) * NT + p + k);
+                xo[0] = status ? NAN : xc[2 * e];
+                xo[1] = status ? NAN : xc[2 * e + 1];
+            }
+            PHASE_END(PH_X);
+        }
+    }
+#undef PHASE_END
+    if (tid == 0) {
+        unsigned long long* prof = reinterpret_cast<unsigned long long*>(v.counters + 16);
+        for (int i = 0; i < PH_COUNT; ++i) atomicAdd(&prof[i], (unsigned long long)tph[i]);
     }
 }
 
@@ -720,7 +976,8 @@ struct meemb200_plan {
     std::vector<GeomDesc> geoms;
     int n_slots_geom, n_slots_work;
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
-    size_t smem_geom, smem_freq, smem_dense;
+    size_t smem_geom, smem_freq, smem_dense, smem_chol;
+    int algo;
     int max_tab_threads;
     int64_t max_FK;
     cudaEvent_t ev[4];
@@ -769,7 +1026,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     if (b->n_geom < 1 || b->n_freq < 1) return fail(MEEMB200_EINVAL, "n_geom and n_freq must be >= 1");
     if (!b->reg_off || !b->h || !b->a || !b->d || !b->nmk || !b->n_modes || !b->flag_off || !b->heaving || !b->freq)
         return fail(MEEMB200_EINVAL, "NULL array in MeemBatch");
-    if (b->algo != MEEMB200_ALGO_SCHUR && b->algo != MEEMB200_ALGO_DENSE) return fail(MEEMB200_EINVAL, "unknown algo");
+    if (b->algo != MEEMB200_ALGO_SCHUR && b->algo != MEEMB200_ALGO_DENSE && b->algo != MEEMB200_ALGO_SCHUR_LU) return fail(MEEMB200_EINVAL, "unknown algo");
+    const bool schur = b->algo != MEEMB200_ALGO_DENSE;
     if (b->root_mode != MEEMB200_ROOTS_REFERENCE && b->root_mode != MEEMB200_ROOTS_CONVERGED) return fail(MEEMB200_EINVAL, "unknown root_mode");
     if (b->freq_kind != MEEMB200_FREQ_OMEGA && b->freq_kind != MEEMB200_FREQ_M0) return fail(MEEMB200_EINVAL, "unknown freq_kind");
     const int G = b->n_geom, F = b->n_freq;
@@ -822,20 +1080,24 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         gd.root_set = s;
         gd.tab_off = tab_tot; tab_tot += table_doubles(L);
         gd.gs_off = gs_tot; gs_tot += gs_doubles(gd.N, R);
-        if (b->want_x && b->algo == MEEMB200_ALGO_SCHUR) { gd.xg_off = xg_tot; xg_tot += (int64_t)gd.p * (gd.N + R); }
+        if (b->want_x && schur) { gd.xg_off = xg_tot; xg_tot += (int64_t)gd.p * (gd.N + R); }
         else gd.xg_off = -1;
         gd.out_rr = n_rr; n_rr += (int64_t)F * R * R;
         gd.out_r = n_r; n_r += (int64_t)F * R;
         gd.out_sys = (int64_t)gi * F;
         gd.out_x = n_x; if (b->want_x) n_x += (int64_t)F * R * gd.NT;
         slot_geom = std::max<int64_t>(slot_geom, (int64_t)gd.p * (gd.p + gd.N + R));
-        slot_freq = std::max<int64_t>(slot_freq, freq_slot_doubles(gd.N, gd.K, R));
+        slot_freq = std::max<int64_t>(slot_freq, std::max(freq_slot_doubles(gd.N, gd.K, R), freq2_slot_doubles(gd.N, gd.K, R)));
         slot_dense = std::max<int64_t>(slot_dense, 2LL * gd.NT * (gd.NT + R));
         max_p = std::max(max_p, gd.p); max_K = std::max(max_K, gd.K); max_NT = std::max(max_NT, gd.NT); max_N = std::max(max_N, gd.N);
         const double p_ = gd.p, N_ = gd.N, K_ = gd.K, NT_ = gd.NT, R_ = R;
-        if (b->algo == MEEMB200_ALGO_SCHUR) {
+        if (schur) {
             cost[gi] = 2.0 / 3.0 * p_ * p_ * p_ + 2.0 * p_ * p_ * (N_ + R_);
-            const double per_f = 2.0 * N_ * N_ * K_ + 2.0 * N_ * K_ * K_ + 2.0 / 3.0 * K_ * K_ * K_ + 2.0 * K_ * K_ * (1 + 2 * R_) + 4.0 * N_ * K_ * R_;
+            // frequency stage: T = H Imk (2N^2K) + lower triangle of Imk^T T (N K^2) + Cholesky (K^3/3) + solves, or
+            // for the pivoted-LU variant the full second GEMM (2NK^2) and LU (2K^3/3)
+            const double per_f = b->algo == MEEMB200_ALGO_SCHUR
+                ? 2.0 * N_ * N_ * K_ + N_ * K_ * K_ + 1.0 / 3.0 * K_ * K_ * K_ + 2.0 * K_ * K_ * (1 + 2 * R_) + 4.0 * N_ * K_ * R_
+                : 2.0 * N_ * N_ * K_ + 2.0 * N_ * K_ * K_ + 2.0 / 3.0 * K_ * K_ * K_ + 2.0 * K_ * K_ * (1 + 2 * R_) + 4.0 * N_ * K_ * R_;
             flops += cost[gi] + per_f * F;
             cost[gi] += per_f * F;
         } else {
@@ -856,7 +1118,12 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->nb_geom = pick_nb<double>(max_p, limit, 4096);
     P->nb_freq = pick_nb<double>(max_K, limit / 2 > 100 * 1024 ? limit / 2 - 8192 : limit, 24 * 1024);
     P->nb_dense = pick_nb<cplx>(max_NT, limit, 4096);
-    if ((b->algo == MEEMB200_ALGO_SCHUR && (!P->nb_geom || !P->nb_freq)) || (b->algo == MEEMB200_ALGO_DENSE && !P->nb_dense)) {
+    P->algo = b->algo;
+    int max_R = 1;
+    for (int gi = 0; gi < G; ++gi) max_R = std::max(max_R, P->geoms[gi].R);
+    P->smem_chol = freq2_smem_bytes(max_K, max_R);
+    if (schur && P->smem_chol > limit) { delete P; return fail(MEEMB200_EINVAL, "exterior mode count too large for the shared-memory Cholesky panel"); }
+    if ((schur && (!P->nb_geom || !P->nb_freq)) || (b->algo == MEEMB200_ALGO_DENSE && !P->nb_dense)) {
         delete P;
         return fail(MEEMB200_EINVAL, "system too large for the shared-memory LU panels");
     }
@@ -866,8 +1133,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     const int sms = ctx->sm_count;
     const int64_t n_sys = (int64_t)G * F;
     P->n_slots_geom = (int)std::min<int64_t>(G, sms);
-    if (b->algo == MEEMB200_ALGO_SCHUR) {
-        const int per_sm = (P->smem_freq + 24 * 1024 <= limit / 2) ? 2 : 1;
+    if (schur) {
+        const int per_sm = (std::max(P->smem_freq + 24 * 1024, P->smem_chol + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
     } else {
         P->n_slots_work = (int)std::min<int64_t>(n_sys, sms);
@@ -891,7 +1158,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     const size_t blob_bytes = off;
     // workspace
     size_t w = 0;
-    H.ws_counters = w; w = align_up(w + 64, 256);
+    H.ws_counters = w; w = align_up(w + 256, 256);
     H.ws_roots = w; w = align_up(w + 8 * (size_t)roots_tot, 256);
     H.ws_tables = w; w = align_up(w + 8 * (size_t)tab_tot, 256);
     H.ws_gstore = w; w = align_up(w + 8 * (size_t)gs_tot, 256);
@@ -900,7 +1167,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     H.slot_doubles_freq = (slot_freq + 31) & ~31LL;
     H.slot_doubles_dense = (slot_dense + 31) & ~31LL;
     size_t slots_bytes;
-    if (b->algo == MEEMB200_ALGO_SCHUR)
+    if (schur)
         slots_bytes = 8 * (size_t)std::max<int64_t>(H.slot_doubles_geom * P->n_slots_geom, H.slot_doubles_freq * P->n_slots_work);
     else
         slots_bytes = 8 * (size_t)(H.slot_doubles_dense * P->n_slots_work);
@@ -920,7 +1187,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
-    P->info.n_launches = (b->algo == MEEMB200_ALGO_SCHUR) ? 5 : 4;
+    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 6 : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->info.flops = flops;
     *out = P;
     return MEEMB200_OK;
@@ -959,9 +1226,16 @@ template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* i
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
-    cudaError_t e = cudaFuncSetAttribute(k_freq<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_freq);
+    cudaError_t e = cudaFuncSetAttribute(k_freq_lu<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_freq);
     if (e != cudaSuccess) return e;
-    k_freq<NB><<<P->n_slots_work, 256, P->smem_freq, s>>>(in, ws, o);
+    if (P->algo == MEEMB200_ALGO_SCHUR) {
+        e = cudaFuncSetAttribute(k_freq_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_chol);
+        if (e != cudaSuccess) return e;
+        k_freq_chol<<<P->n_slots_work, 256, P->smem_chol, s>>>(in, ws, o);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    k_freq_lu<NB><<<P->n_slots_work, 256, P->smem_freq, s>>>(in, ws, o, P->algo == MEEMB200_ALGO_SCHUR ? 1 : 0);
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_dense(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
@@ -973,7 +1247,7 @@ template <int NB> static cudaError_t launch_dense(meemb200_plan* P, const void* 
 
 static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cudaStream_t s) {
     const BlobHeader* h = P->hdr();
-    CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 64, s));
+    CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 256, s));
     const int nt = h->n_sets * h->n_freq;
     k_m0<<<(nt + 127) / 128, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
@@ -1002,7 +1276,7 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
     CUDA_TRY(cudaEventRecord(P->ev[1], s));
     k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
-    if (h->algo == MEEMB200_ALGO_SCHUR) {
+    if (h->algo != MEEMB200_ALGO_DENSE) {
         CUDA_TRY(P->nb_geom == 8 ? launch_geom<8>(P, d_in, d_ws, s) : P->nb_geom == 4 ? launch_geom<4>(P, d_in, d_ws, s) : launch_geom<2>(P, d_in, d_ws, s));
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
         CUDA_TRY(P->nb_freq == 8 ? launch_freq<8>(P, d_in, d_ws, o, s) : P->nb_freq == 4 ? launch_freq<4>(P, d_in, d_ws, o, s) : launch_freq<2>(P, d_in, d_ws, o, s));
@@ -1017,6 +1291,16 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
 extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[3]) {
     if (!P || !ms || !P->ev_ok) return fail(MEEMB200_EINVAL, "no solve recorded");
     for (int i = 0; i < 3; ++i) CUDA_TRY(cudaEventElapsedTime(&ms[i], P->ev[i], P->ev[i + 1]));
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_phase_profile(meemb200_plan* P, const void* d_ws, double cycles[8], void* stream) {
+    if (!P || !d_ws || !cycles) return fail(MEEMB200_EINVAL, "NULL argument");
+    unsigned long long raw[8];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CUDA_TRY(cudaMemcpyAsync(raw, static_cast<const char*>(d_ws) + P->hdr()->ws_counters + 64, sizeof(raw), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    for (int i = 0; i < 8; ++i) cycles[i] = (double)raw[i];
     return MEEMB200_OK;
 }
 

@@ -19,6 +19,10 @@ def ofb():
     return ofb
 
 
+def _algo(ofb, name):
+    return {"schur": ofb.ALGO_SCHUR, "schur_lu": ofb.ALGO_SCHUR_LU, "dense": ofb.ALGO_DENSE}[name]
+
+
 def _check(out, ref, tol=1e-10):
     for var in ("added_mass", "damping", "excitation_force"):
         r = ref[var]
@@ -55,7 +59,7 @@ def test_device_bessel_and_roots(ofb):
                 assert relerr(nk[i], mo.N_k_array(ref_m0[i], h, ref_mk)) <= 1e-9
 
 
-@pytest.mark.parametrize("algo", ["schur", "dense"])
+@pytest.mark.parametrize("algo", ["schur", "schur_lu", "dense"])
 @pytest.mark.parametrize("name", sorted(META1))
 def test_single_solves_vs_reference(ofb, name, algo):
     """A, b, X and coefficients for the golden (case, heaving body, m0) set, m0 injected."""
@@ -63,7 +67,7 @@ def test_single_solves_vs_reference(ofb, name, algo):
     nb = max(c["body_map"]) + 1
     geo = ofb.FlatGeometry.from_body_map(c["h"], c["a"], c["d"], c["NMK"], c["body_map"], list(range(nb)))
     plan = ofb.BatchPlan([geo], c["m0"], freq_kind=ofb.FREQ_M0, want_x=True,
-                         algo=ofb.ALGO_SCHUR if algo == "schur" else ofb.ALGO_DENSE)
+                         algo=_algo(ofb, algo))
     res = plan.run()[0]
     assert np.all(res["status"] == 0)
     for mi, m0 in enumerate(c["m0"]):
@@ -91,12 +95,12 @@ def test_single_solves_vs_reference(ofb, name, algo):
                 assert not np.isfinite(res["excitation_force"][mi, body])
 
 
-@pytest.mark.parametrize("algo", ["schur", "dense"])
+@pytest.mark.parametrize("algo", ["schur", "schur_lu", "dense"])
 @pytest.mark.parametrize("name", sorted(META2))
 def test_sweeps_vs_run_and_store_results(ofb, name, algo):
     s = META2[name]
     geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
-    res = ofb.solve_batch([geo], s["omegas"], algo=ofb.ALGO_SCHUR if algo == "schur" else ofb.ALGO_DENSE, want_x=True)[0]
+    res = ofb.solve_batch([geo], s["omegas"], algo=_algo(ofb, algo), want_x=True)[0]
     assert relerr(res["m0"], Z2[f"{name}/m0"]) <= 2e-14
     ref = {v: Z2[f"{name}/{v}"] for v in ("added_mass", "damping", "excitation_force", "excitation_phase")}
     _check(res, ref)
@@ -117,7 +121,7 @@ def test_m0_infinite_limit(ofb):
     flags = [1, 1]
     X = mo.solve_single(geo_o, flags, np.inf)
     ref = mo.hydro_coefficients(geo_o, X, np.inf, [flags])[0]
-    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_DENSE):
+    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_SCHUR_LU, ofb.ALGO_DENSE):
         geo = ofb.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [12, 12, 12], [flags])
         res = ofb.solve_batch([geo], [np.inf], freq_kind=ofb.FREQ_M0, algo=algo, want_x=True)[0]
         assert relerr(res["added_mass"][0, 0, 0], ref["real"]) <= 1e-10
@@ -153,7 +157,7 @@ def test_heterogeneous_batch_vs_oracle(ofb):
         geos.append(ofb.FlatGeometry(h, a, d, NMK))
         ogeos.append(mo.FlatGeometry(h, a, d, NMK))
     om = np.linspace(0.3, 2.5, 5)
-    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_DENSE):
+    for algo in (ofb.ALGO_SCHUR, ofb.ALGO_SCHUR_LU, ofb.ALGO_DENSE):
         res = ofb.solve_batch(geos, om, algo=algo)
         for g, og in zip(res, ogeos):
             ref = mo.run_sweep(og, om, [0] * og.M, [0])
