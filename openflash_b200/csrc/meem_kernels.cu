@@ -18,6 +18,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -26,6 +27,7 @@
 #include "meem_forms.cuh"
 #include "meem_lu.cuh"
 #include "meem_chol.cuh"
+#include "meem_geom_coop.cuh"
 
 using namespace meem;
 
@@ -299,6 +301,125 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
                 xg[e] = W[(long)r * ld + p + c];
             }
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, geometry stage, grid-cooperative variant (few large geometries): see meem_geom_coop.cuh.
+// Slot 0 holds W [p][ld] followed by the panel scratch (Lbuf [p][16], L11 [256], moves).
+__host__ __device__ inline int64_t coop_ld(int p, int N, int R) { return (p + N + R + 1) & ~1; }
+__host__ __device__ inline int64_t coop_slot_doubles(int p, int N, int R) {
+    return (int64_t)p * coop_ld(p, N, R) + (int64_t)p * kCoopNB + kCoopNB * kCoopNB + 2 * kCoopMaxMoves + 16;
+}
+__host__ __device__ inline size_t coop_smem_bytes(int p) { return sizeof(double) * (size_t)kCoopNB * (size_t)((p + 31) & ~31); }
+
+__global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob, void* ws) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ CoopShared S;
+    DevView v = make_view(blob, ws);
+    double* dsm = reinterpret_cast<double*>(smem);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31;
+    const long gtid = (long)blockIdx.x * nthr + tid, gthr = (long)gridDim.x * nthr;
+    const long gwarp = gtid >> 5, gnwarp = gthr >> 5;
+    for (int item = 0; item < v.hdr->n_geom; ++item) {
+        const int gi = v.order[item];
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        if (tid == 0) { make_layout(g, L); S.status = 0; }
+        __syncthreads();
+        const int p = gd.p, N = gd.N, R = gd.R, M = gd.M;
+        const int ncols = p + N + R;
+        const long ld = coop_ld(p, N, R);
+        double* W = v.slots;
+        CoopScratch sc;
+        sc.Lbuf = W + (int64_t)p * ld;
+        sc.L11g = sc.Lbuf + (int64_t)p * kCoopNB;
+        sc.moves = reinterpret_cast<int*>(sc.L11g + kCoopNB * kCoopNB);
+        const double* tab = v.tables + gd.tab_off;
+        const uint8_t* flags = v.flags + gd.flag_off;
+        double* gs = v.gstore + gd.gs_off;
+        const int ldn = pad8(N);
+        double* HT = gs;
+        double* wv = HT + (int64_t)N * ldn;
+        double* uv = wv + (int64_t)R * N;
+        double* s0 = uv + (int64_t)R * N;
+        double* phi = s0 + R * R;
+        double* bc = phi + R;
+        double* st = bc + R;
+        for (int64_t i = gtid; i < (int64_t)p * ld; i += gthr) W[i] = 0.0;
+        if (gtid == 0) st[0] = 0.0;
+        grid.sync();
+        fill_A_static<double>(g, L, tab, W, ld, (int)gtid, (int)gthr);
+        for (int n = (int)gtid; n < N; n += (int)gthr) W[(long)(L.pot_row[M - 1] + n) * ld + p + n] = 1.0;   // E
+        for (int i = 0; i < R; ++i) fill_b_static<double>(g, L, flags + (int64_t)i * (M + 1), W + p + N + i, ld, (int)gtid, (int)gthr);
+        grid.sync();
+        const int prow = (p + 31) & ~31;
+        int pidx = 0;
+        for (int k0 = 0; k0 < p; k0 += kCoopNB, ++pidx) {
+            const int nb = min(kCoopNB, p - k0);
+            const int owner = pidx % gridDim.x;
+            if ((int)blockIdx.x == owner) {
+                coop_panel_factor(W, ld, k0, nb, p - k0, dsm, prow, S, sc);
+                __syncthreads();
+                if (tid == 0 && S.status) { st[0] = (double)((int)st[0] | S.status); S.status = 0; }
+            }
+            grid.sync();
+            coop_panel_update(W, ld, p, ncols, k0, nb, S, sc);
+            grid.sync();
+        }
+        coop_backsolve(W, ld, p, N + R, dsm, S);
+        grid.sync();
+        // reduce to what the frequency stage needs (same quantities as k_geom, grid-strided)
+        const int bd = M - 1;
+        const double* TL = tab + L.tab[bd];
+        const int c1L = L.col[bd], c2L = c1L + N;
+        for (long e = gtid; e < (long)N * N; e += gthr) {
+            const int n = (int)(e / N), n2 = (int)(e - (long)n * N);
+            double hv = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + n2];
+            if (bd > 0) hv += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + n2];
+            HT[(int64_t)n2 * ldn + n] = hv;
+        }
+        for (long e = gtid; e < (long)N * (ldn - N); e += gthr) HT[(int64_t)(e / (ldn - N)) * ldn + N + e % (ldn - N)] = 0.0;
+        for (long e = gtid; e < (long)R * N; e += gthr) {
+            const int i = (int)(e / N), n = (int)(e - (long)i * N);
+            double u = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + N + i];
+            if (bd > 0) u += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + N + i];
+            uv[e] = u;
+        }
+        for (long t = gwarp; t < (long)R * (N + R); t += gnwarp) {
+            const int j = (int)(t / (N + R)), cidx = (int)(t - (long)j * (N + R));
+            const uint8_t* hvj = flags + (int64_t)j * (M + 1);
+            double acc = 0.0;
+            for (int reg = 0; reg < M; ++reg) {
+                if (!hvj[reg]) continue;
+                const int Nr = g.nmk[reg];
+                const double* T8 = tab + L.tab[reg] + 8 * Nr;
+                for (int n = lane; n < Nr; n += 32) {
+                    acc += T8[n] * W[(long)(L.col[reg] + n) * ld + p + cidx];
+                    if (reg > 0) acc += T8[Nr + n] * W[(long)(L.col[reg] + Nr + n) * ld + p + cidx];
+                }
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) {
+                if (cidx < N) wv[j * N + cidx] = acc;
+                else s0[j * R + (cidx - N)] = acc;
+            }
+        }
+        for (long j = gtid; j < R; j += gthr) {
+            phi[j] = phi_sum(g, L, tab, flags + (int64_t)j * (M + 1));
+            bc[j] = b_end_constant(g, flags + (int64_t)j * (M + 1));
+        }
+        if (gd.xg_off >= 0) {
+            double* xg = v.xstore + gd.xg_off;
+            for (int64_t e = gtid; e < (int64_t)p * (N + R); e += gthr) {
+                const int r = (int)(e / (N + R)), c = (int)(e - (int64_t)r * (N + R));
+                xg[e] = W[(long)r * ld + p + c];
+            }
+        }
+        grid.sync();
     }
 }
 
@@ -976,8 +1097,9 @@ struct meemb200_plan {
     std::vector<GeomDesc> geoms;
     int n_slots_geom, n_slots_work;
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
-    size_t smem_geom, smem_freq, smem_dense, smem_chol;
+    size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop;
     int algo;
+    bool use_coop;          // grid-cooperative geometry stage (few large geometries)
     int max_tab_threads;
     int64_t max_FK;
     cudaEvent_t ev[4];
@@ -1127,12 +1249,23 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         delete P;
         return fail(MEEMB200_EINVAL, "system too large for the shared-memory LU panels");
     }
+    {   // cooperative geometry stage when it beats one CTA per geometry (cost model from measured timings:
+        // single CTA ~6e-8 p^3 ms per geometry, cooperative ~1.5e-3 p ms per geometry)
+        const double waves = std::ceil((double)G / ctx->sm_count);
+        P->smem_coop = coop_smem_bytes(max_p);
+        P->use_coop = schur && P->smem_coop + 8192 <= limit && (double)G * 1.5e-3 * max_p < waves * 6e-8 * (double)max_p * max_p * max_p;
+        if (getenv("MEEMB200_NO_COOP")) P->use_coop = false;
+        if (getenv("MEEMB200_FORCE_COOP")) P->use_coop = schur && P->smem_coop + 8192 <= limit;   // tests
+        if (P->use_coop) slot_geom = 0;
+        if (P->use_coop)
+            for (int gi = 0; gi < G; ++gi) slot_geom = std::max<int64_t>(slot_geom, coop_slot_doubles(P->geoms[gi].p, P->geoms[gi].N, P->geoms[gi].R));
+    }
     P->smem_geom = P->nb_geom ? nb_bytes<double>(P->nb_geom, max_p) : 0;
     P->smem_freq = P->nb_freq ? nb_bytes<double>(P->nb_freq, max_K) : 0;
     P->smem_dense = P->nb_dense ? nb_bytes<cplx>(P->nb_dense, max_NT) : 0;
     const int sms = ctx->sm_count;
     const int64_t n_sys = (int64_t)G * F;
-    P->n_slots_geom = (int)std::min<int64_t>(G, sms);
+    P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, sms);
     if (schur) {
         const int per_sm = (std::max(P->smem_freq + 24 * 1024, P->smem_chol + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
@@ -1219,7 +1352,18 @@ extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
     return MEEMB200_OK;
 }
 
+static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(k_geom_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_coop);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_geom_coop, kCoopThreads, P->smem_coop);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    void* args[] = {(void*)&in, (void*)&ws};
+    return cudaLaunchCooperativeKernel((void*)k_geom_coop, dim3(P->ctx->sm_count), dim3(kCoopThreads), args, P->smem_coop, s);
+}
 template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    if (P->use_coop) return launch_geom_coop(P, in, ws, s);
     cudaError_t e = cudaFuncSetAttribute(k_geom<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
     if (e != cudaSuccess) return e;
     k_geom<NB><<<P->n_slots_geom, 512, P->smem_geom, s>>>(in, ws, 0);

@@ -162,3 +162,29 @@ def test_heterogeneous_batch_vs_oracle(ofb):
         for g, og in zip(res, ogeos):
             ref = mo.run_sweep(og, om, [0] * og.M, [0])
             _check(g, ref)
+
+
+@pytest.mark.parametrize("name", sorted(META2))
+def test_cooperative_geometry_stage(ofb, name, monkeypatch):
+    """The grid-cooperative LU of A11 (k_geom_coop, normally chosen only for few large geometries) forced on
+    the golden sweeps: same parity bar as the one-CTA-per-geometry kernel."""
+    monkeypatch.setenv("MEEMB200_FORCE_COOP", "1")
+    s = META2[name]
+    geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
+    res = ofb.solve_batch([geo, geo], s["omegas"], want_x=True)
+    ref = {v: Z2[f"{name}/{v}"] for v in ("added_mass", "damping", "excitation_force", "excitation_phase")}
+    for r in res:
+        assert np.all(r["status"] == 0)
+        _check(r, ref)
+
+
+def test_cooperative_large_system_vs_oracle(ofb):
+    """small_tricylinder at 50 modes/region (p = 250, odd-sized panels at the end) picks the cooperative path
+    by itself; compare with the oracle's dense solve."""
+    og = mo.FlatGeometry(20.0, [5, 10, 15], [15, 10, 5], [50] * 4)
+    om = [0.4, 1.3, 2.9]
+    ref = mo.run_sweep(og, om, [0, 1, 1], [0, 1])
+    geo = ofb.FlatGeometry.from_body_map(20.0, [5, 10, 15], [15, 10, 5], [50] * 4, [0, 1, 1], [0, 1])
+    res = ofb.solve_batch([geo], om)[0]
+    assert np.all(res["status"] == 0)
+    _check(res, ref)
