@@ -113,15 +113,7 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* sm, int
             const int ti = t / ntc, tj = t - ti * ntc;
             const int ri0 = ti * 32, cj0 = tj * 32;
             if (cj0 > ri0 + 31) continue;
-            unsigned mask = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int r0 = ri0 + 8 * i, c0 = cj0 + 8 * j;
-                    if (r0 < nrow && c0 < ncol && (r0 + 7 >= c0)) mask |= 1u << (i * 4 + j);
-                }
-            if (!mask) continue;
+            // unmasked 4 x 4 blocks (straight-line DMMAs); panel rows beyond nrow are zero, stores are bounds-checked
             double acc[4][4][2];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
@@ -137,22 +129,20 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* sm, int
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (mask & (1u << (i * 4 + j))) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                    for (int j = 0; j < 4; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (mask & (1u << (i * 4 + j))) {
-                        const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
-                        if (r < nrow && c < ncol) {
-                            double2* p = reinterpret_cast<double2*>(P + (long)(kb + r) * ld + kb + c);
-                            double2 v = *p;
-                            v.x -= acc[i][j][0]; v.y -= acc[i][j][1];
-                            *p = v;
-                        }
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
+                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j)) {
+                        double2* p = reinterpret_cast<double2*>(P + (long)(kb + r) * ld + kb + c);
+                        double2 v = *p;
+                        v.x -= acc[i][j][0]; v.y -= acc[i][j][1];
+                        *p = v;
                     }
+                }
         }
     }
     __syncthreads();

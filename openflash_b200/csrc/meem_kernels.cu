@@ -55,7 +55,8 @@ struct BlobHeader {
     double rho;
     int64_t off_geom, off_sets, off_a, off_d, off_nmk, off_flags, off_freq, off_order;
     // workspace byte offsets
-    int64_t ws_roots, ws_tables, ws_gstore, ws_xstore, ws_slots, ws_counters;
+    int64_t ws_roots, ws_tables, ws_gstore, ws_xstore, ws_slots, ws_counters, ws_sysbuf;
+    int64_t sys_stride;          // doubles per system buffer (frequency stage, Cholesky path)
     int64_t slot_doubles_geom, slot_doubles_freq, slot_doubles_dense;
 };
 
@@ -74,6 +75,7 @@ struct DevView {   // resolved pointers, built on device from blob + workspace
     double* gstore;
     double* xstore;
     double* slots;
+    double* sysbuf;
     int* counters;
 };
 
@@ -96,6 +98,7 @@ __device__ __forceinline__ DevView make_view(const void* blob, void* ws) {
     v.gstore = reinterpret_cast<double*>(w + h->ws_gstore);
     v.xstore = reinterpret_cast<double*>(w + h->ws_xstore);
     v.slots = reinterpret_cast<double*>(w + h->ws_slots);
+    v.sysbuf = reinterpret_cast<double*>(w + h->ws_sysbuf);
     v.counters = reinterpret_cast<int*>(w + h->ws_counters);
     return v;
 }
@@ -107,11 +110,14 @@ __device__ __forceinline__ Geom geom_of(const DevView& v, const GeomDesc& gd) {
     return g;
 }
 
-// geometry-stage store layout (doubles): HT[N][ldn] | w[R*N] | u[R*N] | s0[R*R] | phi[R] | bc[R] | status
+// geometry-stage store layout (doubles): HT[N][ldn = pad8(N+2R)] | w[R*N] | u[R*N] | s0[R*R] | phi[R] | bc[R] | status
 // ldn = N rounded up to 8 so that rows are 64-byte aligned for the cp.async operand staging.
 __host__ __device__ inline int pad8(int n) { return (n + 7) & ~7; }
+// Columns N .. N+R-1 of HT hold u'_i = u_i + bc_i e_0 and columns N+R .. N+2R-1 hold w_j, so that the frequency
+// stage's T = H Imk GEMM also yields the right-hand sides and q_j = Imk^T w_j (rows N .. N+2R-1 of its output).
+__host__ __device__ inline int gs_ldn(int N, int R) { return pad8(N + 2 * R); }
 __host__ __device__ inline int64_t gs_doubles(int N, int R) {
-    return (((int64_t)N * pad8(N) + 2LL * R * N + (int64_t)R * R + 2 * R + 2) + 7) & ~7LL;
+    return (((int64_t)N * gs_ldn(N, R) + 2LL * R * N + (int64_t)R * R + 2 * R + 2) + 7) & ~7LL;
 }
 
 struct OutPtrs {
@@ -245,7 +251,7 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
         // reduce to what the frequency stage needs
         double* gs = v.gstore + gd.gs_off;
         double* HT = gs;
-        const int ldn = pad8(N);
+        const int ldn = gs_ldn(N, R);
         double* wv = HT + (int64_t)N * ldn;
         double* uv = wv + (int64_t)R * N;
         double* s0 = uv + (int64_t)R * N;
@@ -262,7 +268,6 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
             if (bd > 0) hv += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + n2];
             HT[(int64_t)n2 * ldn + n] = hv;
         }
-        for (int e = tid; e < N * (ldn - N); e += nthr) HT[(int64_t)(e / (ldn - N)) * ldn + N + e % (ldn - N)] = 0.0;
         for (int e = tid; e < R * N; e += nthr) {
             const int i = e / N, n = e - i * N;
             double u = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + N + i];
@@ -294,6 +299,14 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
             bc[j] = b_end_constant(g, flags + (int64_t)j * (M + 1));
         }
         if (tid == 0) st[0] = (double)sh_status;
+        __syncthreads();
+        for (int e = tid; e < N * (ldn - N); e += nthr) {
+            const int n = e / (ldn - N), c = e - n * (ldn - N);
+            double val = 0.0;
+            if (c < R) val = uv[c * N + n] + (n == 0 ? bc[c] : 0.0);
+            else if (c < 2 * R) val = wv[(c - R) * N + n];
+            HT[(int64_t)n * ldn + N + c] = val;
+        }
         if (gd.xg_off >= 0) {     // keep G and y0 for X reconstruction
             double* xg = v.xstore + gd.xg_off;
             for (int64_t e = tid; e < (int64_t)p * (N + R); e += nthr) {
@@ -341,7 +354,7 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
         const double* tab = v.tables + gd.tab_off;
         const uint8_t* flags = v.flags + gd.flag_off;
         double* gs = v.gstore + gd.gs_off;
-        const int ldn = pad8(N);
+        const int ldn = gs_ldn(N, R);
         double* HT = gs;
         double* wv = HT + (int64_t)N * ldn;
         double* uv = wv + (int64_t)R * N;
@@ -382,7 +395,6 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
             if (bd > 0) hv += TL[3 * N + n] * W[(long)(c2L + n) * ld + p + n2];
             HT[(int64_t)n2 * ldn + n] = hv;
         }
-        for (long e = gtid; e < (long)N * (ldn - N); e += gthr) HT[(int64_t)(e / (ldn - N)) * ldn + N + e % (ldn - N)] = 0.0;
         for (long e = gtid; e < (long)R * N; e += gthr) {
             const int i = (int)(e / N), n = (int)(e - (long)i * N);
             double u = TL[2 * N + n] * W[(long)(c1L + n) * ld + p + N + i];
@@ -418,6 +430,14 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
                 const int r = (int)(e / (N + R)), c = (int)(e - (int64_t)r * (N + R));
                 xg[e] = W[(long)r * ld + p + c];
             }
+        }
+        grid.sync();
+        for (long e = gtid; e < (long)N * (ldn - N); e += gthr) {
+            const int n = (int)(e / (ldn - N)), c = (int)(e - (long)n * (ldn - N));
+            double val = 0.0;
+            if (c < R) val = uv[c * N + n] + (n == 0 ? bc[c] : 0.0);
+            else if (c < 2 * R) val = wv[(c - R) * N + n];
+            HT[(int64_t)n * ldn + N + c] = val;
         }
         grid.sync();
     }
@@ -540,7 +560,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
         double* vv = xs + 2 * R * K;              // v_i[n] complex
         const double* gs = v.gstore + gd.gs_off;
         const double* HT = gs;
-        const int ldn = pad8(N);
+        const int ldn = gs_ldn(N, R);
         const double* wv = HT + (int64_t)N * ldn;
         const double* uv = wv + (int64_t)R * N;
         const double* s0 = uv + (int64_t)R * N;
@@ -680,44 +700,41 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Schur path, frequency stage (default): one CTA (256 threads) per (geometry, frequency), DMMA GEMMs
-// + Cholesky.  The exterior index k is stored permuted, kp = k - 1 (k >= 1), k = 0 -> kp = K - 1, so
-// that the single complex diagonal entry sits last and the leading K x K real part is what gets
-// factorised (Sherman-Morrison closes the complex entry; all vector arithmetic stays real).
-// slot layout (doubles): Imk[N][ldk] | T[N][ldk] | P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] |
-//                        ext[ldk] | xc[2*R*K] | vv[2*R*N]
-__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) {
-    const int64_t ldk = pad8(K);
-    return 2LL * N * ldk + (int64_t)(K + R + 1) * ldk + (int64_t)(2 * R + 2) * ldk + 2LL * R * K + 2LL * R * N + 16;
-}
-__host__ __device__ inline size_t freq2_smem_bytes(int K, int R) {
-    const size_t a = kGemmSmemBytes, b = chol_smem_bytes(K, R);
-    return a > b ? a : b;
+// Schur path, frequency stage (default), two kernels per wave of systems:
+//   k_freq_gemm   256 threads, 2 CTAs/SM, throughput-bound: coupling table Imk, T = H Imk and the lower triangle of
+//                 P = Imk^T T - Re(D) on the DMMA pipe; P, the right-hand sides and q_j = Imk^T w_j go to the
+//                 system's buffer in HBM/L2
+//   k_freq_solve  128 threads, many CTAs/SM, latency-bound: Cholesky of P, back-substitution, Sherman-Morrison
+//                 closure of the single complex entry, hydrodynamic coefficients (+ X)
+// Splitting lets each half run at the occupancy it needs (the solve has ~K sequential steps per system and hides
+// its latency only through many systems in flight per SM).
+// The exterior index k is stored permuted, kp = k - 1 (k >= 1), k = 0 -> kp = K - 1, so that the single complex
+// diagonal entry sits last and the leading K x K real part is what gets factorised.
+// gemm slot (doubles): Imk[N][ldk] | T[N][ldk];   system buffer: P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] | misc[8]
+__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * N * pad8(K) + 16; }
+__host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)(K + 3 * R + 2) * pad8(K) + 8; }
+__host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N) {
+    return chol_smem_bytes(K, R) + sizeof(double) * (size_t)(2 * R * K + 2 * R * N);      // + xc, vv for the X path
 }
 
 enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, PH_COUNT };
+#define PHASE_END(ph) do { __syncthreads(); const long long tn_ = clock64(); tph[ph] += tn_ - tprev; tprev = tn_; } while (0)
 
-__global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws, OutPtrs out) {
+__global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws, int item0, int item1, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
-    __shared__ int sh_item, sh_fail;
-    __shared__ double sh_dots[64];
+    __shared__ int sh_item;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
     const int tid = threadIdx.x, nthr = blockDim.x;
-    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
     const int F = v.hdr->n_freq;
-    const int64_t total = (int64_t)v.hdr->n_geom * F;
     double* slot = v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_freq;
-    long long tph[PH_COUNT];
-#pragma unroll
-    for (int i = 0; i < PH_COUNT; ++i) tph[i] = 0;
+    long long tph[4] = {0, 0, 0, 0};
     long long tprev = clock64();
-#define PHASE_END(ph) do { __syncthreads(); const long long tn_ = clock64(); tph[ph] += tn_ - tprev; tprev = tn_; } while (0)
     for (;;) {
-        const int item = next_item(&v.counters[1], &sh_item);
-        if (item >= total) break;
+        const int item = item0 + next_item(counter, &sh_item);
+        if (item >= item1) break;
         const int gi = v.order[item / F], f = item % F;
         const GeomDesc gd = v.geom[gi];
         const Geom g = geom_of(v, gd);
@@ -725,60 +742,98 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
         const double m0 = v.roots[rs.off + f];
         const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
         const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
-        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_fail = 0; }
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); }
         __syncthreads();
-        const int N = gd.N, K = gd.K, R = gd.R, M = gd.M, p = gd.p;
-        const int ldk = pad8(K), ldn = pad8(N);
+        const int N = gd.N, K = gd.K, R = gd.R;
+        const int ldk = pad8(K), ldn = gs_ldn(N, R);
         double* Imk = slot;
         double* T = Imk + (int64_t)N * ldk;
-        double* P = T + (int64_t)N * ldk;
+        double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
+        double* P = sys;
         double* qv = P + (int64_t)(K + R + 1) * ldk;
-        double* xs = qv + (int64_t)R * ldk;
-        double* ext = xs + (int64_t)(R + 1) * ldk;
-        double* xc = ext + ldk;                    // x2_i[k] complex, natural k order
-        double* vv = xc + 2 * R * K;               // v_i[n] complex
+        double* misc = qv + (int64_t)(2 * R + 1) * ldk;
         const double* gs = v.gstore + gd.gs_off;
         const double* HT = gs;
         const double* wv = HT + (int64_t)N * ldn;
         const double* uv = wv + (int64_t)R * N;
-        const double* s0 = uv + (int64_t)R * N;
-        const double* phi = s0 + R * R;
-        const double* bc = phi + R;
-        const int gstatus = (int)bc[R];
-        // 1. coupling table (columns permuted) and exterior diagonal
-        for (int e = tid; e < N * K; e += nthr) {
-            const int n = e / K, kp = e - n * K;
-            const int k = (kp == K - 1) ? 0 : kp + 1;
-            Imk[(long)n * ldk + kp] = imk(n, k, g, ex, mk, Nk);
+        // 1. coupling table (columns permuted) and exterior diagonal (real parts to the last row of P's block, +1)
+        double* ext = P + (int64_t)(K + R) * ldk;
+        // Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
+        //   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
+        // with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
+        // sines, four divisions and a square root.  Both forms carry ~1e-13 absolute argument-rounding noise in the
+        // sines (|theta| eps, theta up to ~1e3); the exact-equality branch |m_k| == lambda is kept.  Row m = 0 and
+        // column k = 0 go through the reference-ordered imk().  (meemb200_assemble keeps imk() for every entry.)
+        const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= 2 * kGemmStageDoubles;
+        if (fast) {
+            double* tmk = sm;               // [K] m_k (permuted)
+            double* tsk = tmk + K;          // sin(m_k L)
+            double* tck = tsk + K;          // cos(m_k L)
+            double* tnk = tck + K;          // sqrt(2 / N_k) / 2
+            double* tlm = tnk + K;          // [N] lambda_m
+            double* tsl = tlm + N;          // sin(lambda_m L)
+            double* tcl = tsl + N;          // cos(lambda_m L)
+            const double Lh = g.h - g.d[g.M - 1];
+            for (int kp = tid; kp < K; kp += nthr) {
+                const int k = (kp == K - 1) ? 0 : kp + 1;
+                const double mv = mk[k];
+                double sv, cv;
+                const double pr = mv * Lh, er = fma(mv, Lh, -pr);     // exact product = pr + er
+                sincos(pr, &sv, &cv);
+                tmk[kp] = mv; tsk[kp] = fma(er, cv, sv); tck[kp] = fma(-er, sv, cv);
+                tnk[kp] = sqrt(2.0 / Nk[k]) * 0.5;
+            }
+            for (int n = tid; n < N; n += nthr) {
+                const double lam = lambda_ni(n, g.M - 1, g);
+                double sv, cv;
+                const double pr = lam * Lh, er = fma(lam, Lh, -pr);
+                sincos(pr, &sv, &cv);
+                tlm[n] = lam; tsl[n] = fma(er, cv, sv); tcl[n] = fma(-er, sv, cv);
+            }
+            __syncthreads();
+            // row m = 0 and column k = 0 (reference-ordered forms), kept out of the main loop so that it stays uniform
+            for (int e = tid; e < K + N - 1; e += nthr) {
+                const int n = (e < K) ? 0 : e - K + 1, kp = (e < K) ? e : K - 1;
+                Imk[(long)n * ldk + kp] = imk(n, (kp == K - 1) ? 0 : kp + 1, g, ex, mk, Nk);
+            }
+            const int K1 = K - 1;
+            for (int e = tid; e < (N - 1) * K1; e += nthr) {
+                const int n = 1 + e / K1, kp = e - (n - 1) * K1;
+                double val;
+                const double mv = tmk[kp], lam = tlm[n];
+                if (fabs(mv) == lam) {
+                    val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
+                } else {
+                    const double a = tsk[kp] * tcl[n], b = tck[kp] * tsl[n];
+                    const double sp = mv + lam, sd = mv - lam;
+                    // (a + b) / sp + (a - b) / sd over the common denominator; near a resonance (|sd| L < 1) the
+                    // difference a - b = sin(sd L) would lose digits to cancellation, so that term goes direct
+                    if (fabs(sd * Lh) < 1.0) val = tnk[kp] * ((a + b) / sp + sin(sd * Lh) / sd);
+                    else val = tnk[kp] * (((a + b) * sd + (a - b) * sp) / (sp * sd));
+                }
+                Imk[(long)n * ldk + kp] = val;
+            }
+        } else {
+            for (int e = tid; e < N * K; e += nthr) {
+                const int n = e / K, kp = e - n * K;
+                const int k = (kp == K - 1) ? 0 : kp + 1;
+                Imk[(long)n * ldk + kp] = imk(n, k, g, ex, mk, Nk);
+            }
         }
         for (int kp = tid; kp < K; kp += nthr) {
             const int k = (kp == K - 1) ? 0 : kp + 1;
             const cplx dg = ext_diag(k, g, ex, mk);
             ext[kp] = dg.re;
-            if (k == 0) sh_dots[63] = dg.im;
+            if (k == 0) misc[0] = dg.im;
         }
         PHASE_END(PH_IMK);
-        // 2. column dots: r_i = -(bc_i Imk[0][:] + Imk^T u_i) (augmented rows of P), q_j = Imk^T w_j
-        for (int t = tid; t < 2 * R * K; t += nthr) {
-            const int vi = t / K, kp = t - vi * K;
-            const double* vec = (vi < R) ? (uv + vi * N) : (wv + (vi - R) * N);
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            int n = 0;
-            for (; n + 3 < N; n += 4) {
-                a0 = fma(Imk[(long)n * ldk + kp], vec[n], a0);
-                a1 = fma(Imk[(long)(n + 1) * ldk + kp], vec[n + 1], a1);
-                a2 = fma(Imk[(long)(n + 2) * ldk + kp], vec[n + 2], a2);
-                a3 = fma(Imk[(long)(n + 3) * ldk + kp], vec[n + 3], a3);
-            }
-            for (; n < N; ++n) a0 = fma(Imk[(long)n * ldk + kp], vec[n], a0);
-            const double acc = (a0 + a1) + (a2 + a3);
-            if (vi < R) P[(long)(K + vi) * ldk + kp] = -(bc[vi] * Imk[kp] + acc);
-            else qv[(long)(vi - R) * ldk + kp] = acc;
-        }
-        PHASE_END(PH_DOTS);
-        // 3. T = H Imk
-        cta_gemm_dmma(HT, ldn, Imk, ldk, N, K, N, false, sm, [&](int m, int n, double v0, double v1) {
-            if (m < N && n < K) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
+        // 2./3. [T ; -r_i ; q_j] = [H | u'_i | w_j]^T-contraction with Imk: rows N.. of the product are the right-hand
+        // sides r_i = -(bc_i Imk[0][:] + Imk^T u_i) (augmented rows of P) and q_j = Imk^T w_j
+        cta_gemm_dmma(HT, ldn, Imk, ldk, N + 2 * R, K, N, false, sm, [&](int m, int n, double v0, double v1) {
+            if (n >= K) return;
+            if (m < N) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
+            else if (m < N + R) *reinterpret_cast<double2*>(P + (long)(K + m - N) * ldk + n) = make_double2(-v0, -v1);
+            else if (m < N + 2 * R) *reinterpret_cast<double2*>(qv + (long)(m - N - R) * ldk + n) = make_double2(v0, v1);
         });
         PHASE_END(PH_GEMM1);
         // 4. P = Imk^T T - Re(D), lower triangle
@@ -790,9 +845,51 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
             }
         });
         PHASE_END(PH_GEMM2);
+    }
+    if (tid == 0) {
+        unsigned long long* prof = reinterpret_cast<unsigned long long*>(v.counters + 16);
+        for (int i = 0; i < 4; ++i) atomicAdd(&prof[i], (unsigned long long)tph[i]);
+    }
+}
+
+__global__ void __launch_bounds__(128, 4) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    __shared__ int sh_item, sh_fail;
+    __shared__ double sh_dots[64];
+    DevView v = make_view(blob, ws);
+    double* sm = reinterpret_cast<double*>(smem);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int F = v.hdr->n_freq;
+    long long tph[4] = {0, 0, 0, 0};
+    long long tprev = clock64();
+    for (;;) {
+        const int item = item0 + next_item(counter, &sh_item);
+        if (item >= item1) break;
+        const int gi = v.order[item / F], f = item % F;
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        const RootSet rs = v.sets[gd.root_set];
+        const double m0 = v.roots[rs.off + f];
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_fail = 0; }
+        __syncthreads();
+        const int N = gd.N, K = gd.K, R = gd.R, M = gd.M, p = gd.p;
+        const int ldk = pad8(K), ldn = gs_ldn(N, R);
+        double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
+        double* P = sys;
+        double* qv = P + (int64_t)(K + R + 1) * ldk;
+        double* xs = qv + (int64_t)R * ldk;
+        const double* misc = xs + (int64_t)(R + 1) * ldk;
+        const double* gs = v.gstore + gd.gs_off;
+        const double* s0 = gs + (int64_t)N * ldn + 2LL * R * N;
+        const double* phi = s0 + R * R;
+        const double* bc = phi + R;
+        const int gstatus = (int)bc[R];
         // 5. P = L L^T; rows K.. become L^{-1} r_i
         cta_cholesky(P, ldk, K, R, sm, &sh_fail);
-        PHASE_END(PH_CHOL);
+        PHASE_END(0);
         // 6. back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last
         for (int t = tid; t < (R + 1) * K; t += nthr) {
             const int r = t / K, kp = t - r * K;
@@ -800,9 +897,9 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
                                              : (kp == K - 1 ? 1.0 / P[(long)(K - 1) * ldk + K - 1] : 0.0);
         }
         cta_chol_backsolve(P, ldk, K, xs, ldk, R + 1, sm);
-        PHASE_END(PH_BACK);
+        PHASE_END(1);
         // 7. coefficients (eng.py:370-391).  x2_i = w_i + i beta x_e z,  x_e = w_e / (1 - i beta z_e)
-        const double beta = sh_dots[63];
+        const double beta = misc[0];
         const double* zv = xs + (long)R * ldk;
         for (int t = warp; t < R * R + R; t += nwarp) {     // q_j . w_i  and  q_j . z
             const double* qa = qv + (long)((t < R * R) ? t / R : t - R * R) * ldk;
@@ -810,13 +907,13 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
             double a = 0.0;
             for (int k = lane; k < K; k += 32) a = fma(qa[k], xb[k], a);
             a = warp_sum(a);
-            if (lane == 0 && t < 62) sh_dots[t] = a;
+            if (lane == 0 && t < 64) sh_dots[t] = a;
         }
         __syncthreads();
         const int fail = sh_fail;
         const int status = gstatus | (fail ? 4 : 0);
-        const int64_t sys = gd.out_sys + f;
-        if (tid == 0) { out.m0[sys] = m0; out.status[sys] = status; }
+        const int64_t sysi = gd.out_sys + f;
+        if (tid == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
         const double ze = zv[K - 1];
         const double den = 1.0 + beta * beta * ze * ze;
         for (int t = tid; t < R * R; t += nthr) {
@@ -824,7 +921,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
             const double we = xs[(long)i * ldk + K - 1];
             const double xer = we / den, xei = we * beta * ze / den;      // x_e = we (1 + i beta ze) / den
             double qw, qz;
-            if (R * R + R <= 62) { qw = sh_dots[t]; qz = sh_dots[R * R + j]; }
+            if (R * R + R <= 64) { qw = sh_dots[t]; qz = sh_dots[R * R + j]; }
             else {   // many modes: recompute serially (rare)
                 qw = 0.0; qz = 0.0;
                 for (int k = 0; k < K; ++k) {
@@ -849,9 +946,13 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
                 out.phase[o1] = ph;
             }
         }
-        PHASE_END(PH_OUT);
-        // 8. optional X = [y0 + G v ; x2],  v = Imk x2
+        PHASE_END(2);
+        // 8. optional X = [y0 + G v ; x2],  v = Imk x2 (Imk entries recomputed: the gemm kernel's slot is gone)
         if (out.x != nullptr && gd.xg_off >= 0) {
+            const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+            const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+            double* xc = sm + chol_smem_bytes(K, R) / sizeof(double);     // x2_i[k] complex, natural k order
+            double* vv = xc + 2 * R * K;                                  // v_i[n] complex
             for (int e = tid; e < R * K; e += nthr) {
                 const int i = e / K, kp = e - i * K;
                 const int k = (kp == K - 1) ? 0 : kp + 1;
@@ -861,17 +962,22 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
                 xc[2 * (i * K + k) + 1] = beta * xer * zv[kp];
             }
             __syncthreads();
-            for (int t = warp; t < R * N; t += nwarp) {
-                const int i = t / N, n = t - i * N;
-                double ar = 0.0, ai = 0.0;
-                for (int kp = lane; kp < K; kp += 32) {
-                    const int k = (kp == K - 1) ? 0 : kp + 1;
-                    const double c = Imk[(long)n * ldk + kp];
-                    ar = fma(c, xc[2 * (i * K + k)], ar);
-                    ai = fma(c, xc[2 * (i * K + k) + 1], ai);
+            for (int t = warp; t < N; t += nwarp) {
+                double ar[4] = {0, 0, 0, 0}, ai[4] = {0, 0, 0, 0};        // up to 4 modes per pass
+                for (int i0 = 0; i0 < R; i0 += 4) {
+                    for (int q = 0; q < 4; ++q) ar[q] = ai[q] = 0.0;
+                    for (int k = lane; k < K; k += 32) {
+                        const double c = imk(t, k, g, ex, mk, Nk);
+                        for (int q = 0; q < 4 && i0 + q < R; ++q) {
+                            ar[q] = fma(c, xc[2 * ((i0 + q) * K + k)], ar[q]);
+                            ai[q] = fma(c, xc[2 * ((i0 + q) * K + k) + 1], ai[q]);
+                        }
+                    }
+                    for (int q = 0; q < 4 && i0 + q < R; ++q) {
+                        const double sr = warp_sum(ar[q]), si = warp_sum(ai[q]);
+                        if (lane == 0) { vv[2 * ((i0 + q) * N + t)] = sr; vv[2 * ((i0 + q) * N + t) + 1] = si; }
+                    }
                 }
-                ar = warp_sum(ar); ai = warp_sum(ai);
-                if (lane == 0) { vv[2 * t] = ar; vv[2 * t + 1] = ai; }
             }
             __syncthreads();
             const double* xg = v.xstore + gd.xg_off;
@@ -897,15 +1003,15 @@ __global__ void __launch_bounds__(256, 2) k_freq_chol(const void* blob, void* ws
                 xo[0] = status ? NAN : xc[2 * e];
                 xo[1] = status ? NAN : xc[2 * e + 1];
             }
-            PHASE_END(PH_X);
+            PHASE_END(3);
         }
     }
-#undef PHASE_END
     if (tid == 0) {
         unsigned long long* prof = reinterpret_cast<unsigned long long*>(v.counters + 16);
-        for (int i = 0; i < PH_COUNT; ++i) atomicAdd(&prof[i], (unsigned long long)tph[i]);
+        for (int i = 0; i < 4; ++i) atomicAdd(&prof[4 + i], (unsigned long long)tph[i]);
     }
 }
+#undef PHASE_END
 
 // ------------------------------------------------------------------------------------------------
 // dense path: the reference's N_T x N_T complex system, one CTA (512 threads) per (geometry, frequency)
@@ -1100,6 +1206,8 @@ struct meemb200_plan {
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop;
     int algo;
     bool use_coop;          // grid-cooperative geometry stage (few large geometries)
+    int64_t wave_items;     // systems per frequency-stage wave
+    int n_waves, solve_grid;
     int max_tab_threads;
     int64_t max_FK;
     cudaEvent_t ev[4];
@@ -1243,7 +1351,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->algo = b->algo;
     int max_R = 1;
     for (int gi = 0; gi < G; ++gi) max_R = std::max(max_R, P->geoms[gi].R);
-    P->smem_chol = freq2_smem_bytes(max_K, max_R);
+    P->smem_chol = b->want_x ? freq2_solve_smem_bytes(max_K, max_R, max_N) : chol_smem_bytes(max_K, max_R);
     if (schur && P->smem_chol > limit) { delete P; return fail(MEEMB200_EINVAL, "exterior mode count too large for the shared-memory Cholesky panel"); }
     if ((schur && (!P->nb_geom || !P->nb_freq)) || (b->algo == MEEMB200_ALGO_DENSE && !P->nb_dense)) {
         delete P;
@@ -1267,7 +1375,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     const int64_t n_sys = (int64_t)G * F;
     P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, sms);
     if (schur) {
-        const int per_sm = (std::max(P->smem_freq + 24 * 1024, P->smem_chol + 4096) <= limit / 2) ? 2 : 1;
+        const int per_sm = (std::max(P->smem_freq + 24 * 1024, kGemmSmemBytes + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
     } else {
         P->n_slots_work = (int)std::min<int64_t>(n_sys, sms);
@@ -1291,7 +1399,15 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     const size_t blob_bytes = off;
     // workspace
     size_t w = 0;
-    H.ws_counters = w; w = align_up(w + 256, 256);
+    // frequency stage waves: systems per wave bounded by a ~1.5 GB system-buffer budget
+    int64_t sys_stride = 8;
+    for (int gi = 0; gi < G; ++gi) sys_stride = std::max<int64_t>(sys_stride, freq2_sys_doubles(P->geoms[gi].K, P->geoms[gi].R));
+    sys_stride = (sys_stride + 7) & ~7LL;
+    P->wave_items = (int64_t)std::max<int64_t>(4 * P->n_slots_work, (int64_t)(1.5e9 / (8.0 * sys_stride)));
+    P->wave_items = std::min<int64_t>(P->wave_items, n_sys);
+    P->n_waves = b->algo == MEEMB200_ALGO_SCHUR ? (int)((n_sys + P->wave_items - 1) / P->wave_items) : 0;
+    H.sys_stride = sys_stride;
+    H.ws_counters = w; w = align_up(w + 256 + 8 * (size_t)P->n_waves, 256);
     H.ws_roots = w; w = align_up(w + 8 * (size_t)roots_tot, 256);
     H.ws_tables = w; w = align_up(w + 8 * (size_t)tab_tot, 256);
     H.ws_gstore = w; w = align_up(w + 8 * (size_t)gs_tot, 256);
@@ -1305,6 +1421,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     else
         slots_bytes = 8 * (size_t)(H.slot_doubles_dense * P->n_slots_work);
     H.ws_slots = w; w = align_up(w + slots_bytes, 256);
+    H.ws_sysbuf = w; w = align_up(w + (b->algo == MEEMB200_ALGO_SCHUR ? 8 * (size_t)(sys_stride * P->wave_items) : 0), 256);
     P->blob.assign(blob_bytes, 0);
     unsigned char* bp = P->blob.data();
     memcpy(bp, &H, sizeof(H));
@@ -1320,7 +1437,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
-    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 6 : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
+    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 5 + 2 * P->n_waves : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
+    P->solve_grid = 0;
     P->info.flops = flops;
     *out = P;
     return MEEMB200_OK;
@@ -1373,9 +1491,25 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
     cudaError_t e = cudaFuncSetAttribute(k_freq_lu<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_freq);
     if (e != cudaSuccess) return e;
     if (P->algo == MEEMB200_ALGO_SCHUR) {
-        e = cudaFuncSetAttribute(k_freq_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_chol);
+        e = cudaFuncSetAttribute(k_freq_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
         if (e != cudaSuccess) return e;
-        k_freq_chol<<<P->n_slots_work, 256, P->smem_chol, s>>>(in, ws, o);
+        e = cudaFuncSetAttribute(k_freq_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_chol);
+        if (e != cudaSuccess) return e;
+        if (!P->solve_grid) {
+            int per_sm = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_freq_solve, 128, P->smem_chol);
+            if (e != cudaSuccess) return e;
+            P->solve_grid = std::max(1, per_sm) * P->ctx->sm_count;
+        }
+        const BlobHeader* h = P->hdr();
+        int* wave_counters = reinterpret_cast<int*>(static_cast<char*>(ws) + h->ws_counters + 256);
+        const int64_t n_sys = P->info.n_sys;
+        for (int w = 0; w < P->n_waves; ++w) {
+            const int item0 = (int)(w * P->wave_items), item1 = (int)std::min<int64_t>(n_sys, (w + 1) * P->wave_items);
+            const int n = item1 - item0;
+            k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w);
+            k_freq_solve<<<std::min(n, P->solve_grid), 128, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
+        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -1391,7 +1525,7 @@ template <int NB> static cudaError_t launch_dense(meemb200_plan* P, const void* 
 
 static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cudaStream_t s) {
     const BlobHeader* h = P->hdr();
-    CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 256, s));
+    CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 256 + 8 * (size_t)P->n_waves, s));
     const int nt = h->n_sets * h->n_freq;
     k_m0<<<(nt + 127) / 128, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
