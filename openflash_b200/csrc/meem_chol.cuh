@@ -23,14 +23,64 @@ constexpr int kCholLdP = kCholNB + 4;   // 20 = 4 (mod 16): conflict-free fragme
 
 __host__ __device__ inline size_t chol_smem_bytes(int K, int naug) {
     const int rows = ((K + naug + 31) / 32) * 32;
-    return sizeof(double) * ((size_t)kCholNB * (kCholNB + 1) + kCholNB + (size_t)rows * kCholLdP);
+    return sizeof(double) * ((size_t)kCholNB * (kCholNB + 1) + kCholNB + (size_t)kCholNB * kCholLdP + (size_t)rows * kCholLdP);
+}
+// doubles of the per-system store of inverted diagonal blocks (used by the back-substitution)
+__host__ __device__ inline int chol_linv_doubles(int K) { return ((K + kCholNB - 1) / kCholNB) * kCholNB * kCholNB; }
+
+// Cholesky of one 16 x 16 diagonal block by one warp, rows in registers (lane i owns row i), then its inverse.
+// Dg (shared, [16][17]) holds the block on entry (identity-padded beyond nb); on exit Dg = L11 with the RECIPROCAL
+// diagonal, Li (shared, [16][20]) = L11^{-1} (row-major, zero above the diagonal).
+__device__ __forceinline__ void warp_chol16(double* Dg, double* Li, int* fail) {
+    const int lane = threadIdx.x & 31;
+    const int row = lane & 15;
+    double r[kCholNB];
+#pragma unroll
+    for (int c = 0; c < kCholNB; ++c) r[c] = Dg[row * (kCholNB + 1) + c];
+    int bad = 0;
+#pragma unroll
+    for (int j = 0; j < kCholNB; ++j) {
+        const double d = __shfl_sync(0xffffffffu, r[j], j);
+        if (!(d > 0.0) || d == INFINITY) bad |= (d == d && fabs(d) != INFINITY) ? 1 : 2;
+        const double rinv = rsqrt(d);
+        const double lij = r[j] * rinv;               // lane j: sqrt(d)
+        if (row == j) r[j] = rinv;                    // reciprocal diagonal
+        else r[j] = lij;
+#pragma unroll
+        for (int c = j + 1; c < kCholNB; ++c) {
+            const double lcj = __shfl_sync(0xffffffffu, lij, c);
+            if (row >= c) r[c] = fma(-lij, lcj, r[c]);
+        }
+    }
+    if (bad && lane == 0) atomicOr(fail, bad);
+    if (lane < kCholNB) {
+#pragma unroll
+        for (int c = 0; c < kCholNB; ++c) Dg[row * (kCholNB + 1) + c] = (c <= row) ? r[c] : 0.0;
+    }
+    __syncwarp();
+    // inverse: lane c solves L x = e_c  (x[i] = 0 for i < c)
+    if (lane < kCholNB) {
+        double x[kCholNB];
+#pragma unroll
+        for (int i = 0; i < kCholNB; ++i) {
+            double acc = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+            for (int q = 0; q < kCholNB; ++q)
+                if (q < i) acc = fma(-Dg[i * (kCholNB + 1) + q], x[q], acc);
+            x[i] = acc * Dg[i * (kCholNB + 1) + i];
+        }
+#pragma unroll
+        for (int i = 0; i < kCholNB; ++i) Li[i * kCholLdP + lane] = x[i];       // Linv[i][c]
+    }
 }
 
-// returns through *fail (shared int, OR-ed): bit 0 non-positive pivot, bit 1 non-finite pivot
-__device__ void cta_cholesky(double* P, int ld, int K, int naug, double* sm, int* fail) {
+// returns through *fail (shared int, OR-ed): bit 0 non-positive pivot, bit 1 non-finite pivot.
+// On exit the lower triangle of P holds L with the RECIPROCAL of its diagonal on the diagonal, rows K.. hold
+// (L^{-1} r_i)^T, and LI (global, chol_linv_doubles(K)) holds the inverses of the 16 x 16 diagonal blocks.
+__device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, double* sm, int* fail) {
     double* Dg = sm;                                   // [16][17]
-    double* rd = Dg + kCholNB * (kCholNB + 1);         // reciprocal diagonal of the current block
-    double* Pn = rd + kCholNB;                         // [rows][20] current panel L21
+    double* Li = Dg + kCholNB * (kCholNB + 1) + kCholNB;   // [16][20] inverse of the current diagonal block
+    double* Pn = Li + kCholNB * kCholLdP;              // [rows][20] current panel L21
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
     const int lr = lane >> 2, lc = lane & 3;
@@ -44,143 +94,125 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* sm, int
             Dg[i * (kCholNB + 1) + c] = (i < nb && c <= i) ? P[(long)(k0 + i) * ld + k0 + c] : (i == c ? 1.0 : 0.0);
         }
         __syncthreads();
-        if (warp == 0) {
-            for (int j = 0; j < nb; ++j) {
-                const double d = Dg[j * (kCholNB + 1) + j];
-                if (lane == 0) {
-                    if (!(d == d) || fabs(d) == INFINITY) atomicOr(fail, 2);
-                    else if (!(d > 0.0)) atomicOr(fail, 1);
-                }
-                const double s = sqrt(d);
-                const double rinv = 1.0 / s;
-                double lij = 0.0;
-                if (lane > j && lane < nb) {
-                    lij = Dg[lane * (kCholNB + 1) + j] * rinv;
-                    Dg[lane * (kCholNB + 1) + j] = lij;
-                }
-                if (lane == j) { Dg[j * (kCholNB + 1) + j] = s; rd[j] = rinv; }
-                __syncwarp();
-                if (lane > j && lane < nb) {
-                    for (int c = j + 1; c <= lane; ++c)
-                        Dg[lane * (kCholNB + 1) + c] = fma(-lij, Dg[c * (kCholNB + 1) + j], Dg[lane * (kCholNB + 1) + c]);
-                }
-                __syncwarp();
-            }
-            if (lane >= nb && lane < kCholNB) rd[lane] = 1.0;
-        }
+        if (warp == 0) warp_chol16(Dg, Li, fail);
         __syncthreads();
-        // factor block back to the slot (back-substitution reads it there)
-        for (int idx = tid; idx < nb * nb; idx += nthr) {
-            const int i = idx / nb, c = idx - i * nb;
-            if (c <= i) P[(long)(k0 + i) * ld + k0 + c] = Dg[i * (kCholNB + 1) + c];
+        // factor block (reciprocal diagonal) back to the slot, inverse to the LI store
+        for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {
+            const int i = idx >> 4, c = idx & 15;
+            if (i < nb && c <= i) P[(long)(k0 + i) * ld + k0 + c] = Dg[i * (kCholNB + 1) + c];
+            LI[(long)(k0 / kCholNB) * kCholNB * kCholNB + idx] = Li[i * kCholLdP + c];
         }
         const int nrow = KR - kb;
         if (nrow <= 0) break;
         const int ncol = K - kb;
         const int prow = ((nrow + 31) / 32) * 32;
-        // panel solve: L21 = A21 L11^{-T}
-        for (int ri = tid; ri < prow; ri += nthr) {
-            double l[kCholNB];
-            if (ri < nrow) {
-                double* src = P + (long)(kb + ri) * ld + k0;
+        // panel solve on the DMMA pipe: L21 = A21 Linv^T, A fragments straight from L2
+        {
+            double bf[kCholNB / 4][2];
 #pragma unroll
-                for (int c = 0; c < kCholNB; c += 2) {
-                    const double2 v = *reinterpret_cast<const double2*>(src + c);
-                    l[c] = v.x; l[c + 1] = v.y;
+            for (int ks = 0; ks < kCholNB / 4; ++ks)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) bf[ks][j] = Li[(8 * j + lr) * kCholLdP + ks * 4 + lc];   // b[k=q][n=c] = Linv[c][q]
+            for (int rb = warp; rb < prow / 8; rb += nwarp) {
+                const int ri = rb * 8 + lr;
+                const double* src = P + (long)(kb + ri) * ld + k0;
+                double af[kCholNB / 4];
+#pragma unroll
+                for (int ks = 0; ks < kCholNB / 4; ++ks) af[ks] = (ri < nrow && ks * 4 + lc < nb) ? src[ks * 4 + lc] : 0.0;
+                double c[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+                for (int ks = 0; ks < kCholNB / 4; ++ks)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) dmma(c[j][0], c[j][1], af[ks], bf[ks][j]);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int col = 8 * j + 2 * lc;
+                    *reinterpret_cast<double2*>(Pn + ri * kCholLdP + col) = make_double2(c[j][0], c[j][1]);
+                    if (ri < nrow && col < nb) {
+                        double* dst = P + (long)(kb + ri) * ld + k0 + col;
+                        if (col + 1 < nb) *reinterpret_cast<double2*>(dst) = make_double2(c[j][0], c[j][1]);
+                        else dst[0] = c[j][0];
+                    }
                 }
-#pragma unroll
-                for (int c = 0; c < kCholNB; ++c) {
-                    double a = (c < nb) ? l[c] : 0.0;
-#pragma unroll
-                    for (int q = 0; q < kCholNB; ++q)
-                        if (q < c) a = fma(-l[q], Dg[c * (kCholNB + 1) + q], a);
-                    l[c] = a * rd[c];
-                }
-                for (int c = 0; c < nb; ++c) src[c] = l[c];
-            } else {
-#pragma unroll
-                for (int c = 0; c < kCholNB; ++c) l[c] = 0.0;
             }
-#pragma unroll
-            for (int c = 0; c < kCholNB; c += 2)
-                *reinterpret_cast<double2*>(Pn + ri * kCholLdP + c) = make_double2(l[c], l[c + 1]);
         }
         __syncthreads();
         if (ncol <= 0) continue;
-        // trailing update on the DMMA pipe
-        const int ntr = prow / 32, ntc = (ncol + 31) / 32;
+        // trailing update on the DMMA pipe: 16 x 32 warp tiles of the lower triangle, C tile is the accumulator
+        const int ntr = prow / 16, ntc = (ncol + 31) / 32;
         for (int t = warp; t < ntr * ntc; t += nwarp) {
             const int ti = t / ntc, tj = t - ti * ntc;
-            const int ri0 = ti * 32, cj0 = tj * 32;
-            if (cj0 > ri0 + 31) continue;
-            // unmasked 4 x 4 blocks (straight-line DMMAs); panel rows beyond nrow are zero, stores are bounds-checked
-            double acc[4][4][2];
+            const int ri0 = ti * 16, cj0 = tj * 32;
+            if (cj0 > ri0 + 15 || ri0 >= nrow) continue;
+            double acc[2][4][2];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < 2; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
+                    double2 v = make_double2(0.0, 0.0);
+                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j))
+                        v = *reinterpret_cast<const double2*>(P + (long)(kb + r) * ld + kb + c);
+                    acc[i][j][0] = v.x; acc[i][j][1] = v.y;
+                }
 #pragma unroll
             for (int ks = 0; ks < kCholNB / 4; ++ks) {
-                double af[4], bf[4];
+                double af[2], bf[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) af[i] = Pn[(ri0 + 8 * i + lr) * kCholLdP + ks * 4 + lc];
+                for (int i = 0; i < 2; ++i) af[i] = -Pn[(ri0 + 8 * i + lr) * kCholLdP + ks * 4 + lc];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) bf[j] = Pn[(cj0 + 8 * j + lr) * kCholLdP + ks * 4 + lc];
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < 2; ++i)
 #pragma unroll
                     for (int j = 0; j < 4; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < 2; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
-                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j)) {
-                        double2* p = reinterpret_cast<double2*>(P + (long)(kb + r) * ld + kb + c);
-                        double2 v = *p;
-                        v.x -= acc[i][j][0]; v.y -= acc[i][j][1];
-                        *p = v;
-                    }
+                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j))
+                        *reinterpret_cast<double2*>(P + (long)(kb + r) * ld + kb + c) = make_double2(acc[i][j][0], acc[i][j][1]);
                 }
         }
     }
     __syncthreads();
 }
 
-// Back-substitution L^T X = C for nrhs right-hand sides held as rows of X ([nrhs][ldx], global or
-// shared).  Blocked bottom-up; one warp per right-hand side solves the 16 x 16 diagonal block.
-__device__ void cta_chol_backsolve(const double* P, int ld, int K, double* X, int ldx, int nrhs, double* sm) {
-    double* Dg = sm;                                   // [16][17]
+// Back-substitution L^T X = C for nrhs right-hand sides held as rows of X ([nrhs][ldx]).  Blocked bottom-up with
+// the inverted diagonal blocks: x_b = Linv_bb^T c_b is a 16 x 16 mat-vec (no serial chain), then the rows above
+// are updated.  nrhs <= 8 * blockDim.x / 16.
+__device__ void cta_chol_backsolve(const double* P, int ld, int K, const double* LI, double* X, int ldx, int nrhs) {
     const int tid = threadIdx.x, nthr = blockDim.x;
-    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
     const int nblk = (K + kCholNB - 1) / kCholNB;
     for (int blk = nblk - 1; blk >= 0; --blk) {
         const int k0 = blk * kCholNB;
         const int nb = min(kCholNB, K - k0);
+        const double* Lb = LI + (long)blk * kCholNB * kCholNB;
         __syncthreads();
-        for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {
-            const int i = idx >> 4, c = idx & 15;
-            Dg[i * (kCholNB + 1) + c] = (i < nb && c <= i) ? P[(long)(k0 + i) * ld + k0 + c] : (i == c ? 1.0 : 0.0);
+        double xr[8];                                   // up to 8 passes of nthr / 16 right-hand sides
+        const int c = tid & 15, rstep = nthr >> 4;
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+            const int r = (tid >> 4) + ps * rstep;
+            double x = 0.0;
+            if (r < nrhs && c < nb)
+                for (int q = c; q < nb; ++q) x = fma(Lb[q * kCholNB + c], X[(long)r * ldx + k0 + q], x);
+            xr[ps] = x;
         }
         __syncthreads();
-        for (int r = warp; r < nrhs; r += nwarp) {
-            double c = (lane < nb) ? X[(long)r * ldx + k0 + lane] : 0.0;
-            for (int q = nb - 1; q >= 0; --q) {
-                double x = 0.0;
-                if (lane == q) x = c / Dg[q * (kCholNB + 1) + q];
-                x = __shfl_sync(0xffffffffu, x, q);
-                if (lane == q) c = x;
-                else if (lane < q) c = fma(-Dg[q * (kCholNB + 1) + lane], x, c);
-            }
-            if (lane < nb) X[(long)r * ldx + k0 + lane] = c;
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+            const int r = (tid >> 4) + ps * rstep;
+            if (r < nrhs && c < nb) X[(long)r * ldx + k0 + c] = xr[ps];
         }
         __syncthreads();
         for (int idx = tid; idx < nrhs * k0; idx += nthr) {
-            const int r = idx / k0, j = idx - r * k0;
-            double acc = X[(long)r * ldx + j];
-            for (int q = 0; q < nb; ++q) acc = fma(-P[(long)(k0 + q) * ld + j], X[(long)r * ldx + k0 + q], acc);
-            X[(long)r * ldx + j] = acc;
+            const int rr = idx / k0, j = idx - rr * k0;
+            double acc = X[(long)rr * ldx + j];
+            for (int q = 0; q < nb; ++q) acc = fma(-P[(long)(k0 + q) * ld + j], X[(long)rr * ldx + k0 + q], acc);
+            X[(long)rr * ldx + j] = acc;
         }
     }
     __syncthreads();

@@ -710,9 +710,9 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
 // its latency only through many systems in flight per SM).
 // The exterior index k is stored permuted, kp = k - 1 (k >= 1), k = 0 -> kp = K - 1, so that the single complex
 // diagonal entry sits last and the leading K x K real part is what gets factorised.
-// gemm slot (doubles): Imk[N][ldk] | T[N][ldk];   system buffer: P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] | misc[8]
+// gemm slot (doubles): Imk[N][ldk] | T[N][ldk];   system buffer: P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] | misc[8] | LI[K/16][256]
 __host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * N * pad8(K) + 16; }
-__host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)(K + 3 * R + 2) * pad8(K) + 8; }
+__host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)(K + 3 * R + 2) * pad8(K) + 8 + chol_linv_doubles(K); }
 __host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N) {
     return chol_smem_bytes(K, R) + sizeof(double) * (size_t)(2 * R * K + 2 * R * N);      // + xc, vv for the X path
 }
@@ -852,7 +852,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
     }
 }
 
-__global__ void __launch_bounds__(128, 4) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
+__global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
@@ -888,15 +888,16 @@ __global__ void __launch_bounds__(128, 4) k_freq_solve(const void* blob, void* w
         const double* bc = phi + R;
         const int gstatus = (int)bc[R];
         // 5. P = L L^T; rows K.. become L^{-1} r_i
-        cta_cholesky(P, ldk, K, R, sm, &sh_fail);
+        double* LI = xs + (int64_t)(R + 1) * ldk + 8;
+        cta_cholesky(P, ldk, K, R, LI, sm, &sh_fail);
         PHASE_END(0);
-        // 6. back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last
+        // 6. back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last  (the diagonal of P holds 1 / L_ii)
         for (int t = tid; t < (R + 1) * K; t += nthr) {
             const int r = t / K, kp = t - r * K;
             xs[(long)r * ldk + kp] = (r < R) ? P[(long)(K + r) * ldk + kp]
-                                             : (kp == K - 1 ? 1.0 / P[(long)(K - 1) * ldk + K - 1] : 0.0);
+                                             : (kp == K - 1 ? P[(long)(K - 1) * ldk + K - 1] : 0.0);
         }
-        cta_chol_backsolve(P, ldk, K, xs, ldk, R + 1, sm);
+        cta_chol_backsolve(P, ldk, K, LI, xs, ldk, R + 1);
         PHASE_END(1);
         // 7. coefficients (eng.py:370-391).  x2_i = w_i + i beta x_e z,  x_e = w_e / (1 - i beta z_e)
         const double beta = misc[0];
