@@ -38,7 +38,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // lower_only: skip 8x8 blocks that lie strictly above the diagonal (m < n for every element).
 // epi(m, n, v0, v1): called once per lane per stored 8x8 block with the two adjacent columns
 // n, n+1 of row m (n is even); bounds (m < Mm, n < Nn, n+1 < Nn) are the callee's to check.
-constexpr int kGemmKC = 16;
+constexpr int kGemmKC = 32;
 constexpr int kGemmTM = 64, kGemmTN = 128;
 constexpr int kGemmLdA = kGemmTM + 4, kGemmLdB = kGemmTN + 4;
 constexpr int kGemmStageDoubles = kGemmKC * (kGemmLdA + kGemmLdB);
@@ -107,7 +107,10 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
             // warp's blocks inside the tile: rows split in 2, cols in 4 (even split)
             const int tmb = bm1 - bm0, tnb = bn1 - bn0;
             const int rb0 = wr * tmb / 2, rb1 = (wr + 1) * tmb / 2;          // <= 4 blocks
-            const int cb0 = wc * tnb / 4, cb1 = (wc + 1) * tnb / 4;          // <= 4 blocks
+            // column group rotated by warp row, tile and CTA so that the one-block-larger group (uneven splits) does
+            // not always land on the same SM sub-partition (warp w issues on sub-partition w & 3 = wc)
+            const int cg_ = (wc + 2 * wr + ti + tj + (int)blockIdx.x) & 3;
+            const int cb0 = cg_ * tnb / 4, cb1 = (cg_ + 1) * tnb / 4;        // <= 4 blocks
             int nri = rb1 - rb0, nci = cb1 - cb0;
             // lower_only: a warp tile entirely above the diagonal is skipped (warp-uniform)
             if (lower_only && (m0 + rb1 * 8 <= n0 + cb0 * 8)) nri = 0;

@@ -796,22 +796,37 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
                 const int n = (e < K) ? 0 : e - K + 1, kp = (e < K) ? e : K - 1;
                 Imk[(long)n * ldk + kp] = imk(n, (kp == K - 1) ? 0 : kp + 1, g, ex, mk, Nk);
             }
-            const int K1 = K - 1;
-            for (int e = tid; e < (N - 1) * K1; e += nthr) {
-                const int n = 1 + e / K1, kp = e - (n - 1) * K1;
-                double val;
-                const double mv = tmk[kp], lam = tlm[n];
-                if (fabs(mv) == lam) {
-                    val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
-                } else {
-                    const double a = tsk[kp] * tcl[n], b = tck[kp] * tsl[n];
-                    const double sp = mv + lam, sd = mv - lam;
-                    // (a + b) / sp + (a - b) / sd over the common denominator; near a resonance (|sd| L < 1) the
-                    // difference a - b = sin(sd L) would lose digits to cancellation, so that term goes direct
-                    if (fabs(sd * Lh) < 1.0) val = tnk[kp] * ((a + b) / sp + sin(sd * Lh) / sd);
-                    else val = tnk[kp] * (((a + b) * sd + (a - b) * sp) / (sp * sd));
+            // interior: one row per warp, lanes over the columns, branch-free except the exact-equality case.
+            //   (a + b) / sp + S / sd  over the common denominator, S = sin(sd L):  a - b away from a resonance,
+            //   x sinc(x) (Taylor, |x| = |sd L| < 1) near one, where a - b would lose digits to cancellation
+            {
+                const int lane_ = tid & 31, warp_ = tid >> 5, nwarp_ = nthr >> 5;
+                for (int n = 1 + warp_; n < N; n += nwarp_) {
+                    const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
+                    double* row = Imk + (long)n * ldk;
+                    for (int kp = lane_; kp < K - 1; kp += 32) {
+                        const double mv = tmk[kp];
+                        const double a = tsk[kp] * cl, b = tck[kp] * sl;
+                        const double sp = mv + lam, sd = mv - lam;
+                        const double x = sd * Lh, x2 = x * x;
+                        double S = a - b;
+                        if (fabs(x) < 1.0) {
+                            double pl = -8.22063524662432972e-18;                       // -1/19!
+                            pl = fma(pl, x2, 2.81145725434552076e-15);                  //  1/17!
+                            pl = fma(pl, x2, -7.64716373181981648e-13);                 // -1/15!
+                            pl = fma(pl, x2, 1.60590438368216146e-10);                  //  1/13!
+                            pl = fma(pl, x2, -2.50521083854417188e-08);                 // -1/11!
+                            pl = fma(pl, x2, 2.75573192239858907e-06);                  //  1/9!
+                            pl = fma(pl, x2, -1.98412698412698413e-04);                 // -1/7!
+                            pl = fma(pl, x2, 8.33333333333333333e-03);                  //  1/5!
+                            pl = fma(pl, x2, -1.66666666666666667e-01);                 // -1/3!
+                            S = fma(x * x2, pl, x);
+                        }
+                        double val = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
+                        if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
+                        row[kp] = val;
+                    }
                 }
-                Imk[(long)n * ldk + kp] = val;
             }
         } else {
             for (int e = tid; e < N * K; e += nthr) {
