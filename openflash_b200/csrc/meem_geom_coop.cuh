@@ -33,7 +33,9 @@ struct CoopShared {
     double L11[kCoopNB][kCoopNB + 1];
     double top[kCoopNB][8];
     double Us[kCoopNB][12];
+    double xrow[2][kCoopNB];          // pivot-row / row-j exchange of the register-resident panel factorisation
     int mv_dst[kCoopMaxMoves], mv_src[kCoopMaxMoves];
+    int piv[kCoopNB];
     int n_mv;
     int status;
 };
@@ -41,16 +43,17 @@ struct CoopShared {
 // scratch published by the panel owner (global memory, after the matrix in the slot)
 struct CoopScratch {
     double* Lbuf;     // [rows][16] multipliers of the rows below the panel's diagonal block (panel-local row index)
-    double* L11g;     // [16][16]
+    double* L11g;     // [16][16] inverse of the unit-lower diagonal block L11
     int* moves;       // [0] = n_mv, then dst[32], src[32]
 };
 
-// Panel factorisation by one CTA.  panel: shared memory, column-major [nb][prow], prow >= rows.
+__device__ void coop_publish_block(int k0, int nb, CoopShared& S, const CoopScratch& sc);
+
+// Panel factorisation by one CTA (fallback for panels taller than the register-resident variant handles).  panel: shared memory, column-major [nb][prow], prow >= rows.
 __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, double* panel, int prow,
                                   CoopShared& S, const CoopScratch& sc) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
-    __shared__ int piv[kCoopNB];
     for (int i = tid; i < rows; i += nthr) {
         const double* src = W + (long)(k0 + i) * ld + k0;
         for (int q = 0; q < nb; ++q) panel[q * prow + i] = src[q];
@@ -79,7 +82,7 @@ __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, 
         }
         if (bi >= rows) bi = j;                                  // column of NaNs
         if (tid == 0) {
-            piv[j] = bi;
+            S.piv[j] = bi;
             if (!(best < INFINITY) || best < 0.0) atomicOr(&S.status, 2);
             else if (best == 0.0) atomicOr(&S.status, 1);
         }
@@ -97,37 +100,166 @@ __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, 
         }
     }
     __syncthreads();
-    // publish: U11 -> W, L11 -> scratch, L21 -> Lbuf (zero-padded to 16 columns), net permutation
+    // publish: U11 -> W, strict-lower L11 -> S.L11, L21 -> Lbuf (zero-padded to 16 columns)
     for (int idx = tid; idx < kCoopNB * kCoopNB; idx += nthr) {
         const int i = idx >> 4, q = idx & 15;
-        if (i < nb && q < nb) {
-            if (q >= i) W[(long)(k0 + i) * ld + k0 + q] = panel[q * prow + i];
-            sc.L11g[idx] = (q < i) ? panel[q * prow + i] : 0.0;
-        } else {
-            sc.L11g[idx] = 0.0;
-        }
+        if (i < nb && q < nb && q >= i) W[(long)(k0 + i) * ld + k0 + q] = panel[q * prow + i];
+        S.L11[i][q] = (i < nb && q < i) ? panel[q * prow + i] : 0.0;
     }
     for (int idx = tid; idx < (rows - nb) * kCoopNB; idx += nthr) {
         const int i = nb + (idx >> 4), q = idx & 15;
         sc.Lbuf[(long)i * kCoopNB + q] = (q < nb) ? panel[q * prow + i] : 0.0;
     }
-    if (tid == 0) {
-        // simulate the nb swaps on the (at most 2 nb) rows they touch
-        int idx[kCoopMaxMoves], org[kCoopMaxMoves], n = 0;
-        for (int q = 0; q < nb; ++q) { idx[n] = q; org[n] = q; ++n; }
+    coop_publish_block(k0, nb, S, sc);
+}
+
+// After a panel factorisation: S.L11 holds the unit-lower L11 (strictly-lower part), S.piv the pivots.  Publishes
+// L11^{-1} and the net row permutation.  Called by all threads of the owner CTA.
+__device__ void coop_publish_block(int k0, int nb, CoopShared& S, const CoopScratch& sc) {
+    const int tid = threadIdx.x;
+    __syncthreads();
+    if (tid < kCoopNB) {      // column `tid` of L11^{-1}: x = e_c - strict_lower(L11) x, forward
+        double x[kCoopNB];
+#pragma unroll
+        for (int i = 0; i < kCoopNB; ++i) {
+            double acc = (i == tid) ? 1.0 : 0.0;
+#pragma unroll
+            for (int q = 0; q < kCoopNB; ++q)
+                if (q < i) acc = fma(-S.L11[i][q], x[q], acc);
+            x[i] = acc;
+        }
+#pragma unroll
+        for (int i = 0; i < kCoopNB; ++i) sc.L11g[i * kCoopNB + tid] = x[i];
+    }
+    if (tid >= 32 && tid < 64) {      // warp 1: net permutation of the nb swaps on the (<= 2 nb) rows they touch
+        const int lane = tid & 31;
+        int idx = (lane < nb) ? lane : -1, org = idx, n = nb;
         for (int j = 0; j < nb; ++j) {
-            const int pr = piv[j];
-            int b = -1;
-            for (int s = 0; s < n; ++s) if (idx[s] == pr) { b = s; break; }
-            if (b < 0) { idx[n] = pr; org[n] = pr; b = n++; }
-            const int t = org[j]; org[j] = org[b]; org[b] = t;
+            const int pr = S.piv[j];
+            const unsigned hit = __ballot_sync(0xffffffffu, idx == pr);
+            int b;
+            if (hit) b = __ffs(hit) - 1;
+            else { b = n++; if (lane == b) { idx = pr; org = pr; } }
+            const int oj = __shfl_sync(0xffffffffu, org, j), ob = __shfl_sync(0xffffffffu, org, b);
+            if (lane == j) org = ob;
+            if (lane == b) org = oj;
         }
         // the first nb entries are always the top rows (possibly identity moves): the update phase needs them
-        int m = 0;
-        for (int s = 0; s < n; ++s)
-            if (s < nb || org[s] != idx[s]) { sc.moves[1 + m] = k0 + idx[s]; sc.moves[1 + kCoopMaxMoves + m] = k0 + org[s]; ++m; }
-        sc.moves[0] = m;
+        const bool keep = (lane < n) && (lane < nb || org != idx);
+        const unsigned km = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            const int m = __popc(km & ((1u << lane) - 1u));
+            sc.moves[1 + m] = k0 + idx;
+            sc.moves[1 + kCoopMaxMoves + m] = k0 + org;
+        }
+        if (lane == 0) sc.moves[0] = __popc(km);
     }
+}
+
+// Register-resident panel factorisation: thread t owns rows t, t + nthr, ... (RPT of them) with their 16 panel
+// entries in registers; per column one warp-shuffle arg-max, two block barriers and a 2 x 16-double row exchange
+// through shared memory.  rows <= RPT * blockDim.x.
+template <int RPT>
+__device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int rows, CoopShared& S, const CoopScratch& sc) {
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    double r[RPT][kCoopNB];
+#pragma unroll
+    for (int t = 0; t < RPT; ++t) {
+        const int i = tid + t * nthr;
+        const double* src = W + (long)(k0 + i) * ld + k0;
+#pragma unroll
+        for (int q = 0; q < kCoopNB; ++q) r[t][q] = (i < rows && q < nb) ? src[q] : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < kCoopNB; ++j) {
+        if (j >= nb) break;
+        double best = -1.0;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int t = 0; t < RPT; ++t) {
+            const int i = tid + t * nthr;
+            const double v = fabs(r[t][j]);
+            if (i >= j && i < rows && v > best) { best = v; bi = i; }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            const double ov = __shfl_down_sync(0xffffffffu, best, off);
+            const int oi = __shfl_down_sync(0xffffffffu, bi, off);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (lane == 0) { S.wbest[warp] = best; S.widx[warp] = bi; }
+        __syncthreads();
+        best = S.wbest[0]; bi = S.widx[0];
+        for (int w = 1; w < nwarp; ++w) {
+            const double ov = S.wbest[w];
+            const int oi = S.widx[w];
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (bi >= rows) bi = j;                                  // column of NaNs
+        if (tid == 0) {
+            S.piv[j] = bi;
+            if (!(best < INFINITY) || best < 0.0) atomicOr(&S.status, 2);
+            else if (best == 0.0) atomicOr(&S.status, 1);
+        }
+#pragma unroll
+        for (int t = 0; t < RPT; ++t) {
+            const int i = tid + t * nthr;
+            if (i == bi) {
+#pragma unroll
+                for (int q = 0; q < kCoopNB; ++q) S.xrow[0][q] = r[t][q];
+            }
+            if (i == j) {
+#pragma unroll
+                for (int q = 0; q < kCoopNB; ++q) S.xrow[1][q] = r[t][q];
+            }
+        }
+        __syncthreads();
+        if (bi != j) {
+#pragma unroll
+            for (int t = 0; t < RPT; ++t) {
+                const int i = tid + t * nthr;
+                if (i == j) {
+#pragma unroll
+                    for (int q = 0; q < kCoopNB; ++q) r[t][q] = S.xrow[0][q];
+                } else if (i == bi) {
+#pragma unroll
+                    for (int q = 0; q < kCoopNB; ++q) r[t][q] = S.xrow[1][q];
+                }
+            }
+        }
+        const double pv = S.xrow[0][j];
+#pragma unroll
+        for (int t = 0; t < RPT; ++t) {
+            const int i = tid + t * nthr;
+            if (i > j && i < rows) {
+                const double l = r[t][j] / pv;
+                r[t][j] = l;
+#pragma unroll
+                for (int q = 0; q < kCoopNB; ++q)
+                    if (q > j) r[t][q] = fma(-l, S.xrow[0][q], r[t][q]);
+            }
+        }
+    }
+    // publish: U11 -> W, strict-lower L11 -> S.L11, L21 -> Lbuf (zero beyond nb)
+#pragma unroll
+    for (int t = 0; t < RPT; ++t) {
+        const int i = tid + t * nthr;
+        if (i < kCoopNB) {
+#pragma unroll
+            for (int q = 0; q < kCoopNB; ++q) S.L11[i][q] = (i < nb && q < i) ? r[t][q] : 0.0;
+        }
+        if (i < nb) {
+#pragma unroll
+            for (int q = 0; q < kCoopNB; ++q)
+                if (q < nb && q >= i) W[(long)(k0 + i) * ld + k0 + q] = r[t][q];
+        } else if (i < rows) {
+            double2* dst = reinterpret_cast<double2*>(sc.Lbuf + (long)i * kCoopNB);
+#pragma unroll
+            for (int q = 0; q < kCoopNB; q += 2) dst[q >> 1] = make_double2(r[t][q], r[t][q + 1]);
+        }
+    }
+    coop_publish_block(k0, nb, S, sc);
 }
 
 // Update phase of one panel, run by every CTA on its own 8-column chunks of the columns >= kb.
@@ -158,46 +290,54 @@ __device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, 
             if (s < nb) S.top[s][cc] = val;
         }
         __syncthreads();
-        // 2. U12 = L11^{-1} A12, one thread per column
-        if (tid < 8) {
-            double u[kCoopNB];
-#pragma unroll
-            for (int q = 0; q < kCoopNB; ++q) {
-                double a = (q < nb && tid < cw) ? S.top[q][tid] : 0.0;
+        // 2. U12 = L11^{-1} A12: thread (q, column) takes one dot product with row q of the inverse
+        if (tid < kCoopNB * 8) {
+            const int q = tid >> 3, cx = tid & 7;
+            double a = 0.0;
+            if (q < nb && cx < cw) {
 #pragma unroll
                 for (int q2 = 0; q2 < kCoopNB; ++q2)
-                    if (q2 < q) a = fma(-S.L11[q][q2], u[q2], a);
-                u[q] = a;
-                S.Us[q][tid] = a;
-                if (q < nb && tid < cw) W[(long)(k0 + q) * ld + col0 + tid] = a;
+                    if (q2 <= q) a = fma(S.L11[q][q2], S.top[q2][cx], a);
+                W[(long)(k0 + q) * ld + col0 + cx] = a;
             }
+            S.Us[q][cx] = a;
         }
         __syncthreads();
-        // 3. A22 -= L21 U12 (8-row blocks per warp, A fragments straight from L2)
+        // 3. A22 -= L21 U12 (8-row blocks per warp, A fragments straight from L2, four blocks in flight per warp)
         const int nrb = (rows_below + 7) >> 3;
         double bf[kCoopNB / 4];
 #pragma unroll
         for (int ks = 0; ks < kCoopNB / 4; ++ks) bf[ks] = S.Us[ks * 4 + lc][lr];
-        for (int rb = warp; rb < nrb; rb += nwarp) {
-            const int i = nb + rb * 8 + lr;                  // panel-local row of this lane's A fragment
-            const bool rok = (rb * 8 + lr) < rows_below;
-            double c0 = 0.0, c1 = 0.0;
-            double af[kCoopNB / 4];
+        const int col = col0 + 2 * lc;
+        const bool pair_ok = ((col & 1) == 0);          // ld is even: 16-byte aligned pair (the pad column absorbs col + 1 == ncols)
+        for (int rb0 = warp; rb0 < nrb; rb0 += 4 * nwarp) {
+            double af[4][kCoopNB / 4], cv[4][2];
+            bool rok[4];
 #pragma unroll
-            for (int ks = 0; ks < kCoopNB / 4; ++ks) af[ks] = rok ? sc.Lbuf[(long)i * kCoopNB + ks * 4 + lc] : 0.0;
+            for (int u = 0; u < 4; ++u) {
+                const int rb = rb0 + u * nwarp;
+                rok[u] = (rb < nrb) && (rb * 8 + lr) < rows_below;
+                const long i = nb + rb * 8 + lr;             // panel-local row of this lane's A fragment
 #pragma unroll
-            for (int ks = 0; ks < kCoopNB / 4; ++ks) dmma(c0, c1, af[ks], bf[ks]);
-            const int col = col0 + 2 * lc;
-            if (rok && col < ncols) {
-                double* pw = W + (long)(kb + rb * 8 + lr) * ld + col;
-                if ((col & 1) == 0) {          // ld is even: 16-byte aligned pair (the pad column absorbs col + 1 == ncols)
-                    double2* ptr = reinterpret_cast<double2*>(pw);
-                    double2 v = *ptr;
-                    v.x -= c0; v.y -= c1;
-                    *ptr = v;
-                } else {
-                    pw[0] -= c0;
-                    if (col + 1 < ncols) pw[1] -= c1;
+                for (int ks = 0; ks < kCoopNB / 4; ++ks) af[u][ks] = rok[u] ? -sc.Lbuf[i * kCoopNB + ks * 4 + lc] : 0.0;
+                cv[u][0] = cv[u][1] = 0.0;
+                if (rok[u] && col < ncols) {
+                    const double* pw = W + (long)(kb + rb * 8 + lr) * ld + col;
+                    if (pair_ok) { const double2 v = *reinterpret_cast<const double2*>(pw); cv[u][0] = v.x; cv[u][1] = v.y; }
+                    else { cv[u][0] = pw[0]; if (col + 1 < ncols) cv[u][1] = pw[1]; }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int ks = 0; ks < kCoopNB / 4; ++ks) dmma(cv[u][0], cv[u][1], af[u][ks], bf[ks]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int rb = rb0 + u * nwarp;
+                if (rok[u] && col < ncols) {
+                    double* pw = W + (long)(kb + rb * 8 + lr) * ld + col;
+                    if (pair_ok) *reinterpret_cast<double2*>(pw) = make_double2(cv[u][0], cv[u][1]);
+                    else { pw[0] = cv[u][0]; if (col + 1 < ncols) pw[1] = cv[u][1]; }
                 }
             }
         }

@@ -375,7 +375,10 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
             const int nb = min(kCoopNB, p - k0);
             const int owner = pidx % gridDim.x;
             if ((int)blockIdx.x == owner) {
-                coop_panel_factor(W, ld, k0, nb, p - k0, dsm, prow, S, sc);
+                const int rows = p - k0;
+                if (rows <= kCoopThreads) coop_panel_factor_reg<1>(W, ld, k0, nb, rows, S, sc);
+                else if (rows <= 2 * kCoopThreads) coop_panel_factor_reg<2>(W, ld, k0, nb, rows, S, sc);
+                else coop_panel_factor(W, ld, k0, nb, rows, dsm, prow, S, sc);
                 __syncthreads();
                 if (tid == 0 && S.status) { st[0] = (double)((int)st[0] | S.status); S.status = 0; }
             }
