@@ -279,7 +279,7 @@ def main():
         peak_dmma = ofb.fp64_peak(1, local_rank)
         peak = max(peak_dfma, peak_dmma)
         st = {k: float(np.mean([x[k] for x in stage])) for k in stage[0]}
-        phase_share = {k: round(v, 4) for k, v in plan.phase_profile().items()} if args.algo == "schur" else None
+        phase_share = {k: (round(v, 4) if isinstance(v, float) else v) for k, v in plan.phase_profile().items()} if args.algo == "schur" else None
         dom = max(("geometry", "frequency"), key=lambda k: st[k])
         K_, N_ = int(flat[0].NMK[-1]), int(flat[0].NMK[-2])
         if args.algo != "dense":

@@ -155,9 +155,11 @@ int meemb200_last_timing(meemb200_plan* plan, float ms[3]);
 
 /* Per-phase SM-cycle totals (summed over CTAs) of the frequency-stage kernel of the most recent
  * meemb200_solve that used `d_workspace`: [0] coupling table, [1] column dots / right-hand sides,
- * [2] T = H Imk, [3] Imk^T T, [4] Cholesky, [5] back-substitution, [6] coefficients, [7] X.
+ * [2] T = H Imk, [3] Imk^T T, [4] Cholesky, [5] back-substitution, [6] coefficients, [7] X;
+ * [8..13] cooperative geometry stage as seen by CTA 0: [8] panel factorisation (owner CTAs), [9] factor + grid
+ * barrier, [10] trailing update, [11] barrier after update, [12] back-substitution, [13] back-substitution + barrier.
  * Synchronises the stream.  Measurement only. */
-int meemb200_phase_profile(meemb200_plan* plan, const void* d_workspace, double cycles[8], void* stream);
+int meemb200_phase_profile(meemb200_plan* plan, const void* d_workspace, double cycles[16], void* stream);
 
 #ifdef __cplusplus
 }

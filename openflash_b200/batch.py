@@ -217,11 +217,13 @@ class BatchPlan:
 
     def phase_profile(self):
         """Share of SM cycles per phase of the frequency-stage kernel of the last solve (measurement only)."""
-        cyc = (C.c_double * 8)()
+        cyc = (C.c_double * 16)()
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.lib.meemb200_phase_profile(self.plan, self.d_ws.data_ptr(), cyc, C.c_void_p(stream)))
-        tot = sum(cyc) or 1.0
-        return {k: cyc[i] / tot for i, k in enumerate(self.PHASES)}
+        tot = sum(cyc[:8]) or 1.0
+        out = {k: cyc[i] / tot for i, k in enumerate(self.PHASES)}
+        out["coop_geom_cycles"] = [cyc[i] for i in range(8, 16)]
+        return out
 
     def download(self):
         """Device->host read of all outputs; returns flat numpy arrays."""

@@ -29,6 +29,7 @@ constexpr int kCoopMaxMoves = 2 * kCoopNB;
 
 struct CoopShared {
     double wbest[kCoopThreads / 32];
+    unsigned long long wkey[kCoopThreads / 32];
     int widx[kCoopThreads / 32];
     double L11[kCoopNB][kCoopNB + 1];
     double top[kCoopNB][8];
@@ -48,6 +49,17 @@ struct CoopScratch {
 };
 
 __device__ void coop_publish_block(int k0, int nb, CoopShared& S, const CoopScratch& sc);
+
+// Warp-wide arg-max of 64-bit keys (bit patterns of non-negative doubles), smallest index among equal keys.
+// On return every lane holds the winning key and index.
+__device__ __forceinline__ void coop_warp_argmax(unsigned long long& key, int& idx) {
+    const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, khi);
+    const unsigned mlo = __reduce_max_sync(0xffffffffu, khi == mhi ? klo : 0u);
+    const bool win = (khi == mhi) && (klo == mlo);
+    idx = (int)__reduce_min_sync(0xffffffffu, win ? (unsigned)idx : 0x7fffffffu);
+    key = ((unsigned long long)mhi << 32) | mlo;
+}
 
 // Panel factorisation by one CTA (fallback for panels taller than the register-resident variant handles).  panel: shared memory, column-major [nb][prow], prow >= rows.
 __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, double* panel, int prow,
@@ -174,32 +186,27 @@ __device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int ro
 #pragma unroll
     for (int j = 0; j < kCoopNB; ++j) {
         if (j >= nb) break;
-        double best = -1.0;
+        // arg-max of |a| with the smallest row index on ties.  |a| >= 0, so the IEEE bit pattern orders like an
+        // unsigned integer and the warp reduction is three redux.sync instead of five double shuffles + compares.
+        unsigned long long key = 0ull;
         int bi = 0x7fffffff;
 #pragma unroll
         for (int t = 0; t < RPT; ++t) {
             const int i = tid + t * nthr;
-            const double v = fabs(r[t][j]);
-            if (i >= j && i < rows && v > best) { best = v; bi = i; }
+            const unsigned long long kv = (unsigned long long)__double_as_longlong(fabs(r[t][j]));
+            if (i >= j && i < rows && (bi == 0x7fffffff || kv > key)) { key = kv; bi = i; }
         }
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-            const double ov = __shfl_down_sync(0xffffffffu, best, off);
-            const int oi = __shfl_down_sync(0xffffffffu, bi, off);
-            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-        }
-        if (lane == 0) { S.wbest[warp] = best; S.widx[warp] = bi; }
+        coop_warp_argmax(key, bi);
+        if (lane == 0) { S.wkey[warp] = key; S.widx[warp] = bi; }
         __syncthreads();
-        best = S.wbest[0]; bi = S.widx[0];
-        for (int w = 1; w < nwarp; ++w) {
-            const double ov = S.wbest[w];
-            const int oi = S.widx[w];
-            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-        }
-        if (bi >= rows) bi = j;                                  // column of NaNs
+        key = (lane < nwarp) ? S.wkey[lane] : 0ull;
+        bi = (lane < nwarp) ? S.widx[lane] : 0x7fffffff;
+        coop_warp_argmax(key, bi);
+        const double best = __longlong_as_double((long long)key);
+        if (bi >= rows) bi = j;                                  // no candidate row
         if (tid == 0) {
             S.piv[j] = bi;
-            if (!(best < INFINITY) || best < 0.0) atomicOr(&S.status, 2);
+            if (!(best < INFINITY)) atomicOr(&S.status, 2);      // inf or NaN pivot column
             else if (best == 0.0) atomicOr(&S.status, 1);
         }
 #pragma unroll
@@ -228,12 +235,12 @@ __device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int ro
                 }
             }
         }
-        const double pv = S.xrow[0][j];
+        const double rpv = 1.0 / S.xrow[0][j];
 #pragma unroll
         for (int t = 0; t < RPT; ++t) {
             const int i = tid + t * nthr;
             if (i > j && i < rows) {
-                const double l = r[t][j] / pv;
+                const double l = r[t][j] * rpv;                  // LAPACK dgetf2 scales by the reciprocal pivot too
                 r[t][j] = l;
 #pragma unroll
                 for (int q = 0; q < kCoopNB; ++q)
@@ -263,7 +270,9 @@ __device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int ro
 }
 
 // Update phase of one panel, run by every CTA on its own 8-column chunks of the columns >= kb.
-__device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, int nb, CoopShared& S, const CoopScratch& sc) {
+__device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, int nb, CoopShared& S, const CoopScratch& sc,
+                                  unsigned long long* tmr) {
+    const long long tu0 = clock64();
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
     const int lr = lane >> 2, lc = lane & 3;
@@ -276,6 +285,8 @@ __device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, 
     __syncthreads();
     const int n_mv = S.n_mv;
     const int rows_below = p - kb;
+    const long long tu1 = clock64();
+    if (tmr && blockIdx.x == 0 && threadIdx.x == 32) tmr[0] += (unsigned long long)(tu1 - tu0);
     for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
         const int col0 = kb + 8 * c;
         const int cw = min(8, ncols - col0);
@@ -290,6 +301,7 @@ __device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, 
             if (s < nb) S.top[s][cc] = val;
         }
         __syncthreads();
+        if (tmr && blockIdx.x == 0 && threadIdx.x == 32 && c == 0) tmr[1] += (unsigned long long)(clock64() - tu1);
         // 2. U12 = L11^{-1} A12: thread (q, column) takes one dot product with row q of the inverse
         if (tid < kCoopNB * 8) {
             const int q = tid >> 3, cx = tid & 7;
@@ -345,55 +357,86 @@ __device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, 
     }
 }
 
-// Back-substitution U x = y for the right-hand-side columns owned by this CTA (no grid sync).
-// ycol: shared memory, p doubles.
+// Back-substitution U x = y for the right-hand-side columns owned by this CTA (no grid sync): the CTA's columns are
+// taken two at a time (shared U traffic), each kept whole in shared memory.  Per 16-row block, bottom-up: the rows
+// of U that the update needs are prefetched into registers while one warp per column solves the 16 x 16 triangle.
+// ycol: shared memory, 2 * p doubles.  p <= 2 * blockDim.x rows per prefetch pass (else the pass repeats).
 __device__ void coop_backsolve(double* W, long ld, int p, int nrhs, double* ycol, CoopShared& S) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5;
     const int nblk = (p + kCoopNB - 1) / kCoopNB;
-    for (int rc = blockIdx.x; rc < nrhs; rc += gridDim.x) {
-        const int col = p + rc;
+    const int pp = (p + kCoopNB - 1) & ~(kCoopNB - 1);          // columns padded with zeros to a whole block
+    double* y0 = ycol;
+    double* y1 = ycol + pp;
+    __shared__ double rdiag[kCoopNB];
+    for (int rc = 2 * blockIdx.x; rc < nrhs; rc += 2 * gridDim.x) {
+        const int colA = p + rc;
+        const bool two = rc + 1 < nrhs;
         __syncthreads();
-        for (int i = tid; i < p; i += nthr) ycol[i] = W[(long)i * ld + col];
+        for (int i = tid; i < pp; i += nthr) {
+            y0[i] = (i < p) ? W[(long)i * ld + colA] : 0.0;
+            y1[i] = (two && i < p) ? W[(long)i * ld + colA + 1] : 0.0;
+        }
         for (int blk = nblk - 1; blk >= 0; --blk) {
             const int k0 = blk * kCoopNB;
             const int nb = min(kCoopNB, p - k0);
-            __syncthreads();
-            for (int idx = tid; idx < kCoopNB * kCoopNB; idx += nthr) {
-                const int q = idx >> 4, c = idx & 15;
-                S.L11[q][c] = (q < nb && c < nb && c >= q) ? W[(long)(k0 + q) * ld + k0 + c] : (q == c ? 1.0 : 0.0);
-            }
-            __syncthreads();
-            if (warp == 0) {
-                double c = (lane < nb) ? ycol[k0 + lane] : 0.0;
-                for (int q = nb - 1; q >= 0; --q) {
-                    double x = 0.0;
-                    if (lane == q) x = c / S.L11[q][q];
-                    x = __shfl_sync(0xffffffffu, x, q);
-                    if (lane == q) c = x;
-                    else if (lane < q) c = fma(-S.L11[lane][q], x, c);
-                }
-                if (lane < nb) ycol[k0 + lane] = c;
-            }
-            __syncthreads();
-            for (int i = tid; i < k0; i += nthr) {
-                const double* urow = W + (long)i * ld + k0;
-                double acc = ycol[i];
-                if (nb == kCoopNB) {
+            // prefetch this thread's first two update rows of U[:, k0 : k0 + 16) (the common case p <= 2 * nthr)
+            double u[2][kCoopNB];
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int i = tid + t * nthr;
+                if (i < k0) {
+                    const double* urow = W + (long)i * ld + k0;
 #pragma unroll
                     for (int q = 0; q < kCoopNB; q += 2) {
                         const double2 u2 = *reinterpret_cast<const double2*>(urow + q);
-                        acc = fma(-u2.x, ycol[k0 + q], acc);
-                        acc = fma(-u2.y, ycol[k0 + q + 1], acc);
+                        u[t][q] = (q < nb) ? u2.x : 0.0; u[t][q + 1] = (q + 1 < nb) ? u2.y : 0.0;
                     }
-                } else {
-                    for (int q = 0; q < nb; ++q) acc = fma(-urow[q], ycol[k0 + q], acc);
                 }
-                ycol[i] = acc;
             }
+            for (int idx = tid; idx < kCoopNB * kCoopNB; idx += nthr) {
+                const int q = idx >> 4, c = idx & 15;
+                const double v = (q < nb && c < nb && c >= q) ? W[(long)(k0 + q) * ld + k0 + c] : (q == c ? 1.0 : 0.0);
+                S.L11[q][c] = v;
+                if (q == c) rdiag[q] = 1.0 / v;
+            }
+            __syncthreads();
+            if (warp < 2) {
+                double* y = warp ? y1 : y0;
+                double c = (lane < nb) ? y[k0 + lane] : 0.0;
+                for (int q = nb - 1; q >= 0; --q) {
+                    const double x = __shfl_sync(0xffffffffu, c * rdiag[q], q);
+                    if (lane == q) c = x;
+                    else if (lane < q) c = fma(-S.L11[lane][q], x, c);
+                }
+                if (lane < nb) y[k0 + lane] = c;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int i = tid + t * nthr;
+                if (i < k0) {
+                    double a0 = y0[i], a1 = y1[i];
+#pragma unroll
+                    for (int q = 0; q < kCoopNB; ++q) {
+                        a0 = fma(-u[t][q], y0[k0 + q], a0);
+                        a1 = fma(-u[t][q], y1[k0 + q], a1);
+                    }
+                    y0[i] = a0; y1[i] = a1;
+                }
+            }
+            for (int i = tid + 2 * nthr; i < k0; i += nthr) {     // tall systems: remaining rows straight from L2
+                const double* urow = W + (long)i * ld + k0;
+                double a0 = y0[i], a1 = y1[i];
+                for (int q = 0; q < nb; ++q) { a0 = fma(-urow[q], y0[k0 + q], a0); a1 = fma(-urow[q], y1[k0 + q], a1); }
+                y0[i] = a0; y1[i] = a1;
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        for (int i = tid; i < p; i += nthr) W[(long)i * ld + col] = ycol[i];
+        for (int i = tid; i < p; i += nthr) {
+            W[(long)i * ld + colA] = y0[i];
+            if (two) W[(long)i * ld + colA + 1] = y1[i];
+        }
     }
 }
 

@@ -337,6 +337,7 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
     const int lane = tid & 31;
     const long gtid = (long)blockIdx.x * nthr + tid, gthr = (long)gridDim.x * nthr;
     const long gwarp = gtid >> 5, gnwarp = gthr >> 5;
+    unsigned long long* cprof = reinterpret_cast<unsigned long long*>(v.counters + 16) + 8;
     for (int item = 0; item < v.hdr->n_geom; ++item) {
         const int gi = v.order[item];
         const GeomDesc gd = v.geom[gi];
@@ -374,6 +375,7 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
         for (int k0 = 0; k0 < p; k0 += kCoopNB, ++pidx) {
             const int nb = min(kCoopNB, p - k0);
             const int owner = pidx % gridDim.x;
+            long long tq0 = clock64();
             if ((int)blockIdx.x == owner) {
                 const int rows = p - k0;
                 if (rows <= kCoopThreads) coop_panel_factor_reg<1>(W, ld, k0, nb, rows, S, sc);
@@ -381,13 +383,24 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
                 else coop_panel_factor(W, ld, k0, nb, rows, dsm, prow, S, sc);
                 __syncthreads();
                 if (tid == 0 && S.status) { st[0] = (double)((int)st[0] | S.status); S.status = 0; }
+                if (tid == 0) atomicAdd(&cprof[0], (unsigned long long)(clock64() - tq0));
             }
             grid.sync();
-            coop_panel_update(W, ld, p, ncols, k0, nb, S, sc);
+            long long tq1 = clock64();
+            if (gtid == 32) cprof[1] += (unsigned long long)(tq1 - tq0);          // factor + barrier, seen by a non-owner warp of CTA 0
+            coop_panel_update(W, ld, p, ncols, k0, nb, S, sc, cprof + 6);
+            __syncthreads();
+            long long tq2 = clock64();
+            if (gtid == 32) cprof[2] += (unsigned long long)(tq2 - tq1);          // update (CTA 0's share)
             grid.sync();
+            if (gtid == 32) cprof[3] += (unsigned long long)(clock64() - tq2);    // barrier after update
         }
+        long long tq3 = clock64();
         coop_backsolve(W, ld, p, N + R, dsm, S);
+        __syncthreads();
+        if (gtid == 32) cprof[4] += (unsigned long long)(clock64() - tq3);
         grid.sync();
+        if (gtid == 32) cprof[5] += (unsigned long long)(clock64() - tq3);
         // reduce to what the frequency stage needs (same quantities as k_geom, grid-strided)
         const int bd = M - 1;
         const double* TL = tab + L.tab[bd];
@@ -1591,13 +1604,13 @@ extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[3]) {
     return MEEMB200_OK;
 }
 
-extern "C" int meemb200_phase_profile(meemb200_plan* P, const void* d_ws, double cycles[8], void* stream) {
+extern "C" int meemb200_phase_profile(meemb200_plan* P, const void* d_ws, double cycles[16], void* stream) {
     if (!P || !d_ws || !cycles) return fail(MEEMB200_EINVAL, "NULL argument");
-    unsigned long long raw[8];
+    unsigned long long raw[16];
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     CUDA_TRY(cudaMemcpyAsync(raw, static_cast<const char*>(d_ws) + P->hdr()->ws_counters + 64, sizeof(raw), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
-    for (int i = 0; i < 8; ++i) cycles[i] = (double)raw[i];
+    for (int i = 0; i < 16; ++i) cycles[i] = (double)raw[i];
     return MEEMB200_OK;
 }
 
