@@ -152,15 +152,23 @@ def cpu_sample_tasks(geoms, omegas, target_systems):
     return tasks, n_sys
 
 
-def run_cpu(geoms, omegas, target_systems, pool):
+def run_cpu(geoms, omegas, target_systems, pool, min_seconds=0.0, max_seconds=30.0):
+    """Time the oracle on a sample of the workload.  With min_seconds > 0 the sample is repeated (same tasks) until
+    that much wall time has been spent, so that the baseline rests on 10-30 s of CPU work."""
     tasks, n_sys = cpu_sample_tasks(geoms, omegas, target_systems)
     t0 = time.perf_counter()
-    list(pool.map(_cpu_chunk, tasks, chunksize=1))
-    return n_sys, time.perf_counter() - t0
+    done = 0
+    while True:
+        list(pool.map(_cpu_chunk, tasks, chunksize=1))
+        done += n_sys
+        el = time.perf_counter() - t0
+        if el >= min_seconds or el * 2 > max_seconds:
+            break
+    return done, time.perf_counter() - t0
 
 
 def cpu_target(name):
-    return {"big_tricylinder": 32, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64 * 2}[name]
+    return {"big_tricylinder": 512, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64}[name]
 
 
 # ------------------------------------------------------------------------------------------ main
@@ -196,7 +204,7 @@ def main():
                 run_cpu(geoms, omegas, min(cores, cpu_target(args.workload)), pool)
             tot_sys, tot_t = 0, 0.0
             for _ in range(args.steps):
-                n, t = run_cpu(geoms, omegas, cpu_target(args.workload), pool)
+                n, t = run_cpu(geoms, omegas, cpu_target(args.workload), pool, min_seconds=10.0 / max(args.steps, 1))
                 tot_sys += n
                 tot_t += t
         val = tot_sys / tot_t
@@ -280,35 +288,48 @@ def main():
         peak = max(peak_dfma, peak_dmma)
         st = {k: float(np.mean([x[k] for x in stage])) for k in stage[0]}
         phase_share = {k: (round(v, 4) if isinstance(v, float) else v) for k, v in plan.phase_profile().items()} if args.algo == "schur" else None
-        dom = max(("geometry", "frequency"), key=lambda k: st[k])
-        K_, N_ = int(flat[0].NMK[-1]), int(flat[0].NMK[-2])
-        if args.algo != "dense":
-            def per_f(g):   # closed-form flops of the frequency stage actually executed (kernel table)
-                N, K, R = float(g.NMK[-2]), float(g.NMK[-1]), float(g.R)
-                if args.algo == "schur":
-                    return 2 * N * N * K + N * K * K + K ** 3 / 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R
-                return 2 * N * N * K + 2 * N * K * K + 2 / 3 * K ** 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R
-            freq_flops = sum(len(omegas) * per_f(g) for g in flat)
-            geom_flops = float(plan.info.flops) - freq_flops
-            kflops = freq_flops if dom == "frequency" else geom_flops
-            kname = ("k_freq_chol" if args.algo == "schur" else "k_freq_lu") if dom == "frequency" else "k_geom"
-        else:
-            kflops = float(plan.info.flops)
-            kname = "k_dense"
-            dom = "frequency"
+        F_ = len(omegas)
+
+        def kernel_flops(g):   # closed-form real FP64 flops per kernel for geometry g (kernel table)
+            N, K, R, p = float(g.NMK[-2]), float(g.NMK[-1]), float(g.R), float(g.size - g.NMK[-1])
+            NT = float(g.size)
+            if args.algo == "dense":
+                return {"frequency": F_ * (8 / 3 * NT ** 3 + 8 * NT * NT * R)}
+            geom = 2 / 3 * p ** 3 + 2 * p * p * (N + R)
+            if args.algo == "schur":
+                return {"geometry": geom, "freq_gemm": F_ * (2 * N * N * K + N * K * K),
+                        "freq_solve": F_ * (K ** 3 / 3 + 2 * K * K * (R + 1) + 4 * K * R)}
+            return {"geometry": geom, "frequency": F_ * (2 * N * N * K + 2 * N * K * K + 2 / 3 * K ** 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R)}
+        kf = {}
+        for g in flat:
+            for k, v in kernel_flops(g).items():
+                kf[k] = kf.get(k, 0.0) + v
+        if args.algo == "schur" and st.get("freq_solve", 0.0) == 0.0:      # several waves: only the combined stage was timed
+            kf = {"geometry": kf["geometry"], "frequency": kf["freq_gemm"] + kf["freq_solve"]}
+        dom = max(kf, key=lambda k: st[k])
+        kname = {"geometry": "k_geom_coop/k_geom", "freq_gemm": "k_freq_gemm", "freq_solve": "k_freq_solve",
+                 "frequency": "k_dense" if args.algo == "dense" else "k_freq_*"}[dom]
+        kflops = kf[dom]
         achieved = kflops / (st[dom] * 1e-3)
-        roofline = {"bound": "fp64", "kernel": kname, "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None,
+        traffic = None
+        try:     # DRAM bytes per launch of the dominant kernel from the committed ncu capture of this workload
+            with open(os.path.join(ROOT, "profiles", "ncu_summary.json")) as fh:
+                traffic = json.load(fh).get(args.workload, {}).get(kname, {}).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        roofline = {"bound": "tensor", "pipe": "FP64 DMMA (mma.sync m8n8k4 f64; tcgen05 has no FP64 kind)", "kernel": kname,
+                    "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                     "peak_source": "measured in this run: max(DFMA register loop %.1f, DMMA m8n8k4 %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
                                    % (peak_dfma / 1e12, peak_dmma / 1e12),
                     "flops_per_launch": kflops, "kernel_ms": st[dom], "stage_ms": st, "phase_share": phase_share,
+                    "step_fp64_frac": sum(kf.values()) / (sum(st[k] for k in ("roots", "geometry", "frequency")) * 1e-3) / peak,
                     "dense_equivalent_tflops": value * (8.0 / 3.0 * flat[0].size ** 3 + 8.0 * flat[0].size ** 2 * flat[0].R) / 1e12}
         cpu = None
         if not args.no_cpu and world == 1:
             import multiprocessing as mp
             with mp.get_context("fork").Pool(cores) as pool:
                 run_cpu(geoms, omegas, min(cores, cpu_target(args.workload)), pool)
-                n, t = run_cpu(geoms, omegas, cpu_target(args.workload), pool)
+                n, t = run_cpu(geoms, omegas, cpu_target(args.workload), pool, min_seconds=10.0)
             cpu = {"value": n / t, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": f"{n} systems sampled evenly from the workload, oracle (numpy/scipy restatement of the reference path), {cores} processes x 1 BLAS thread, {t:.1f} s"}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),

@@ -149,9 +149,11 @@ int meemb200_bessel(meemb200_ctx* ctx, int32_t kind, int64_t n, const double* d_
 int meemb200_fp64_peak(meemb200_ctx* ctx, int32_t kind, double* flops, void* stream);
 
 /* Duration (ms) of the stages of the most recent meemb200_solve on this plan, measured with CUDA
- * events on the launching stream: ms[0] roots, ms[1] geometry stage, ms[2] frequency stage.
+ * events on the launching stream: ms[0] roots, ms[1] geometry stage, ms[2] frequency stage (all of it),
+ * ms[3] its GEMM kernel k_freq_gemm, ms[4] its solve kernel k_freq_solve (ms[3] = ms[2], ms[4] = 0 when the
+ * frequency stage ran in more than one wave or not on the Cholesky path).
  * Only valid after the stream has been synchronised. */
-int meemb200_last_timing(meemb200_plan* plan, float ms[3]);
+int meemb200_last_timing(meemb200_plan* plan, float ms[5]);
 
 /* Per-phase SM-cycle totals (summed over CTAs) of the frequency-stage kernel of the most recent
  * meemb200_solve that used `d_workspace`: [0] coupling table, [1] column dots / right-hand sides,

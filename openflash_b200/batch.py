@@ -209,9 +209,9 @@ class BatchPlan:
                                            int(self.info.workspace_bytes), C.byref(self.out), C.c_void_p(stream)))
 
     def stage_ms(self):
-        ms = (C.c_float * 3)()
+        ms = (C.c_float * 5)()
         _lib.check(self.lib.meemb200_last_timing(self.plan, ms))
-        return dict(roots=ms[0], geometry=ms[1], frequency=ms[2])
+        return dict(roots=ms[0], geometry=ms[1], frequency=ms[2], freq_gemm=ms[3], freq_solve=ms[4])
 
     PHASES = ("imk", "dots", "gemm_H_Imk", "gemm_ImkT_T", "cholesky", "backsolve", "coefficients", "x")
 

@@ -1242,7 +1242,7 @@ struct meemb200_plan {
     int n_waves, solve_grid;
     int max_tab_threads;
     int64_t max_FK;
-    cudaEvent_t ev[4];
+    cudaEvent_t ev[6];      // 0 start, 1 after roots, 2 after geometry, 3 after last k_freq_gemm, 4 after last k_freq_solve, 5 end
     bool ev_ok;
 };
 
@@ -1540,7 +1540,9 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
             const int item0 = (int)(w * P->wave_items), item1 = (int)std::min<int64_t>(n_sys, (w + 1) * P->wave_items);
             const int n = item1 - item0;
             k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w);
+            if (w == P->n_waves - 1) cudaEventRecord(P->ev[3], s);
             k_freq_solve<<<std::min(n, P->solve_grid), 128, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
+            if (w == P->n_waves - 1) cudaEventRecord(P->ev[4], s);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -1594,13 +1596,22 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
         CUDA_TRY(P->nb_dense == 8 ? launch_dense<8>(P, d_in, d_ws, o, s) : P->nb_dense == 4 ? launch_dense<4>(P, d_in, d_ws, o, s) : launch_dense<2>(P, d_in, d_ws, o, s));
     }
-    CUDA_TRY(cudaEventRecord(P->ev[3], s));
+    if (h->algo != MEEMB200_ALGO_SCHUR) { CUDA_TRY(cudaEventRecord(P->ev[3], s)); CUDA_TRY(cudaEventRecord(P->ev[4], s)); }
+    CUDA_TRY(cudaEventRecord(P->ev[5], s));
     return MEEMB200_OK;
 }
 
-extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[3]) {
+extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[5]) {
     if (!P || !ms || !P->ev_ok) return fail(MEEMB200_EINVAL, "no solve recorded");
-    for (int i = 0; i < 3; ++i) CUDA_TRY(cudaEventElapsedTime(&ms[i], P->ev[i], P->ev[i + 1]));
+    CUDA_TRY(cudaEventElapsedTime(&ms[0], P->ev[0], P->ev[1]));
+    CUDA_TRY(cudaEventElapsedTime(&ms[1], P->ev[1], P->ev[2]));
+    CUDA_TRY(cudaEventElapsedTime(&ms[2], P->ev[2], P->ev[5]));
+    if (P->algo == MEEMB200_ALGO_SCHUR && P->n_waves == 1) {     // single wave: the two frequency kernels separately
+        CUDA_TRY(cudaEventElapsedTime(&ms[3], P->ev[2], P->ev[3]));
+        CUDA_TRY(cudaEventElapsedTime(&ms[4], P->ev[3], P->ev[4]));
+    } else {
+        ms[3] = ms[2]; ms[4] = 0.0f;
+    }
     return MEEMB200_OK;
 }
 
