@@ -138,6 +138,14 @@ int meemb200_solve_host(meemb200_plan* plan, const MeemOutputs* host_out, void* 
  * Any of A/b/c may be NULL. */
 int meemb200_assemble(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
                       int32_t g, int32_t f, double* d_A, double* d_b, double* d_c, void* stream);
+/* Potential and velocity fields of one solution at n_points points (device pointers): replaces the arithmetic of
+ * MEEMEngine.calculate_potentials / calculate_velocities (meem_engine.py:395-467, :478-553).  X: [NT] complex128
+ * solution of geometry g at frequency index f for radiating mode `mode` (its heaving flags select the particular
+ * solution).  out: 9 planes of n_points doubles: Re phiH, Im phiH, Re vrH, Im vrH, Re vzH, Im vzH, phiP, vrP, vzP.
+ * The region of a point is chosen by r alone; the reference's inside-the-body NaN masks are the caller's to apply. */
+int meemb200_fields(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
+                    int32_t g, int32_t f, int32_t mode, const double* d_X, int64_t n_points,
+                    const double* d_r, const double* d_z, double* d_out, void* stream);
 /* m0[n], mk[n][K], Nk[n][K] for (freq[i], h[i]) pairs; device pointers. */
 int meemb200_roots(meemb200_ctx* ctx, int32_t n, int32_t K, const double* d_freq, const double* d_h,
                    int32_t freq_kind, int32_t root_mode, double* d_m0, double* d_mk, double* d_Nk, void* stream);

@@ -280,6 +280,35 @@ class BatchPlan:
                 np.ascontiguousarray(cc[:, :p]), cc[:, p].real.copy())
 
 
+    def fields(self, X, r, z, g=0, f=0, mode=0):
+        """Raw field values of solution X ([NT] complex) of system (g, f), radiating mode `mode`, at points (r, z):
+        dict(phiH, vrH, vzH complex; phiP, vrP, vzP real), region chosen by r alone (no body masks)."""
+        t = self.torch
+        if not self._uploaded:
+            self.upload()
+        r = np.ascontiguousarray(np.asarray(r, dtype=np.float64).ravel())
+        z = np.ascontiguousarray(np.asarray(z, dtype=np.float64).ravel())
+        n = r.size
+        if z.size != n or n == 0:
+            raise ValueError("r and z must be non-empty and of equal size")
+        Xc = np.ascontiguousarray(np.asarray(X, dtype=np.complex128).ravel())
+        if Xc.size != int(self.NT[g]):
+            raise ValueError("X must have N_T entries")
+        d_X = t.from_numpy(Xc.view(np.float64).copy()).to(self.device)
+        d_r = t.from_numpy(r.copy()).to(self.device)
+        d_z = t.from_numpy(z.copy()).to(self.device)
+        out = t.empty(9 * n, dtype=t.float64, device=self.device)
+        stream = t.cuda.current_stream(self.device).cuda_stream
+        rc = self.lib.meemb200_fields(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(), int(self.info.workspace_bytes),
+                                      int(g), int(f), int(mode), d_X.data_ptr(), n, d_r.data_ptr(), d_z.data_ptr(),
+                                      out.data_ptr(), C.c_void_p(stream))
+        if rc == -1:
+            raise ValueError(self.lib.meemb200_last_error().decode())
+        _lib.check(rc)
+        o = out.cpu().numpy().reshape(9, n)
+        return dict(phiH=o[0] + 1j * o[1], vrH=o[2] + 1j * o[3], vzH=o[4] + 1j * o[5], phiP=o[6].copy(), vrP=o[7].copy(), vzP=o[8].copy())
+
+
 def solve_batch(geometries, freqs, **kw):
     """Convenience: plan, upload, solve, download; returns one result dict per geometry."""
     return BatchPlan(geometries, freqs, **kw).run()
@@ -292,7 +321,7 @@ def device_roots(freq, h, K, *, freq_kind=FREQ_OMEGA, root_mode=ROOTS_REFERENCE,
     ctx = get_context(device)
     dev = torch.device("cuda", device)
     freq = np.atleast_1d(np.asarray(freq, dtype=np.float64))
-    hh = np.ascontiguousarray(np.broadcast_to(np.asarray(h, dtype=np.float64), freq.shape))
+    hh = np.array(np.broadcast_to(np.asarray(h, dtype=np.float64), freq.shape), dtype=np.float64, order="C")
     n = len(freq)
     d_f = torch.from_numpy(np.ascontiguousarray(freq)).to(dev)
     d_h = torch.from_numpy(hh).to(dev)

@@ -1187,6 +1187,122 @@ __global__ void k_assemble(const void* blob, void* ws, int gi, int f, cplx* A, c
 }
 
 // ------------------------------------------------------------------------------------------------
+// Field evaluation: potential and velocity of the homogeneous solution and of the particular
+// solution at arbitrary points, one warp per point, lanes over the harmonics.  Mirrors
+// MEEMEngine.calculate_potentials / calculate_velocities (eng.py:395-467, :478-553) with the radial / vertical
+// eigenfunctions of me.py:192-416 in the reference's operation order; the region is chosen by r alone and the
+// reference's "inside the body" masks are applied by the caller (they are index bookkeeping, not arithmetic).
+// out: 9 planes of n_points doubles: Re/Im phiH, Re/Im vrH, Re/Im vzH, phiP, vrP, vzP.
+__global__ void __launch_bounds__(256) k_fields(const void* blob, void* ws, int gi, int f, int mode, const double* X,
+                                                long n_points, const double* rp, const double* zp, double* out) {
+    __shared__ Layout L;
+    __shared__ Exterior ex;
+    DevView v = make_view(blob, ws);
+    const int F = v.hdr->n_freq;
+    const GeomDesc gd = v.geom[gi];
+    const Geom g = geom_of(v, gd);
+    const RootSet rs = v.sets[gd.root_set];
+    const double m0 = v.roots[rs.off + f];
+    const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+    const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+    if (threadIdx.x == 0) { make_layout(g, L); make_exterior(g, m0, ex); }
+    __syncthreads();
+    const uint8_t* hv = v.flags + gd.flag_off + (int64_t)mode * (gd.M + 1);
+    const int lane = threadIdx.x & 31;
+    const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long)gridDim.x * blockDim.x) >> 5;
+    const int M = g.M;
+    const double h = g.h;
+    for (long pt = wid; pt < n_points; pt += nw) {
+        const double r = rp[pt], z = zp[pt];
+        int reg = M;
+        for (int i = M - 1; i >= 0; --i) if (r <= g.a[i]) reg = i;
+        cplx pH = cmake(0, 0), vr = cmake(0, 0), vz = cmake(0, 0);
+        double pP = 0.0, vrP = 0.0, vzP = 0.0;
+        if (reg < M) {
+            const int i = reg, Ni = g.nmk[i], col = L.col[i];
+            const double ai = g.a[i];
+            for (int n = lane; n < Ni; n += 32) {
+                const cplx c1 = cmake(X[2 * (col + n)], X[2 * (col + n) + 1]);
+                const cplx c2 = (i > 0) ? cmake(X[2 * (col + Ni + n)], X[2 * (col + Ni + n) + 1]) : cmake(0, 0);
+                double R1, dR1, R2 = 0.0, dR2 = 0.0, Zn, dZn;
+                if (n == 0) {
+                    R1 = 0.5; dR1 = 0.0; Zn = 1.0; dZn = 0.0;
+                    if (i > 0) { R2 = 0.5 * log(r / ai); dR2 = (r != 0.0) ? 1.0 / (2.0 * r) : INFINITY; }
+                } else {
+                    const double lam = lambda_ni(n, i, g);
+                    const double den1 = i0e(lam * ai), e1 = exp(lam * (r - ai));
+                    R1 = (r == ai) ? 1.0 : (i0e(lam * r) / den1) * e1;
+                    dR1 = ((lam * i1e(lam * r)) / den1) * e1;
+                    if (i > 0) {
+                        const double den2 = k0e(lam * ai), e2 = exp(lam * (ai - r));
+                        R2 = (r == ai) ? 1.0 : (k0e(lam * r) / den2) * e2;
+                        dR2 = ((-lam * k1e(lam * r)) / den2) * e2;
+                    }
+                    const double arg = lam * (z + h);
+                    Zn = kSqrt2 * cos(arg);
+                    dZn = -lam * kSqrt2 * sin(arg);
+                }
+                const cplx t = cmake(c1.re * R1 + c2.re * R2, c1.im * R1 + c2.im * R2);
+                const cplx dt = cmake(c1.re * dR1 + c2.re * dR2, c1.im * dR1 + c2.im * dR2);
+                pH.re += t.re * Zn; pH.im += t.im * Zn;
+                vr.re += dt.re * Zn; vr.im += dt.im * Zn;
+                vz.re += t.re * dZn; vz.im += t.im * dZn;
+            }
+            if (hv[i]) {                                  // me.py:179-186
+                const double hd = h - g.d[i];
+                pP = (1.0 / (2.0 * hd)) * ((z + h) * (z + h) - (r * r) / 2.0);
+                vrP = -r / (2.0 * hd);
+                vzP = (z + h) / hd;
+            }
+        } else {
+            const int K = L.K, p = L.p;
+            const double aM = g.a[M - 1];
+            for (int k = lane; k < K; k += 32) {
+                const cplx c = cmake(X[2 * (p + k)], X[2 * (p + k) + 1]);
+                cplx Lam, dLam;
+                double Zk, dZk;
+                if (k == 0) {
+                    double j0a, y0a, j1a, y1a, j0, y0, j1, y1;
+                    bessel_jy01(m0 * aM, &j0a, &y0a, &j1a, &y1a);
+                    bessel_jy01(m0 * r, &j0, &y0, &j1, &y1);
+                    const cplx H0a = cmake(j0a, y0a);
+                    Lam = (r == aM) ? cmake(1.0, 0.0) : cmake(j0, y0) / H0a;
+                    dLam = cmake(-(m0 * j1), -(m0 * y1)) / H0a;
+                    if (ex.lowbranch) {
+                        Zk = (1.0 / sqrt(Nk[0])) * cosh(m0 * (z + h));
+                        dZk = (1.0 / sqrt(Nk[0])) * m0 * sinh(m0 * (z + h));
+                    } else {
+                        Zk = sqrt(2.0 * m0 * h) * (exp(m0 * z) + exp(-m0 * (z + 2.0 * h)));
+                        dZk = m0 * sqrt(2.0 * h * m0) * (exp(m0 * z) - exp(-m0 * (z + 2.0 * h)));
+                    }
+                } else {
+                    const double m = mk[k];
+                    const double den = k0e(m * aM), e = exp(m * (aM - r));
+                    Lam = cmake((r == aM) ? 1.0 : (k0e(m * r) / den) * e, 0.0);
+                    dLam = cmake(((-(m * k1e(m * r))) / den) * e, 0.0);
+                    const double isn = 1.0 / sqrt(Nk[k]);
+                    Zk = isn * cos(m * (z + h));
+                    dZk = -isn * m * sin(m * (z + h));
+                }
+                const cplx cl = c * Lam, cd = c * dLam;
+                pH.re += cl.re * Zk; pH.im += cl.im * Zk;
+                vr.re += cd.re * Zk; vr.im += cd.im * Zk;
+                vz.re += cl.re * dZk; vz.im += cl.im * dZk;
+            }
+        }
+        pH.re = warp_sum(pH.re); pH.im = warp_sum(pH.im);
+        vr.re = warp_sum(vr.re); vr.im = warp_sum(vr.im);
+        vz.re = warp_sum(vz.re); vz.im = warp_sum(vz.im);
+        if (lane == 0) {
+            out[0 * n_points + pt] = pH.re; out[1 * n_points + pt] = pH.im;
+            out[2 * n_points + pt] = vr.re; out[3 * n_points + pt] = vr.im;
+            out[4 * n_points + pt] = vz.re; out[5 * n_points + pt] = vz.im;
+            out[6 * n_points + pt] = pP; out[7 * n_points + pt] = vrP; out[8 * n_points + pt] = vzP;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // FP64 throughput microbenchmarks (roofline denominator)
 __global__ void k_dfma_peak(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -1672,6 +1788,26 @@ extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws,
     k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
     k_assemble<<<1, 512, 0, s>>>(d_in, d_ws, g, f, reinterpret_cast<cplx*>(d_A), reinterpret_cast<cplx*>(d_b), reinterpret_cast<cplx*>(d_c));
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_fields(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f, int32_t mode,
+                               const double* d_X, int64_t n_points, const double* d_r, const double* d_z, double* d_out, void* stream) {
+    if (!P || !d_in || !d_ws || !d_X || !d_r || !d_z || !d_out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
+    const BlobHeader* h = P->hdr();
+    if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
+    if (mode < 0 || mode >= P->geoms[g].R) return fail(MEEMB200_EINVAL, "mode index out of range");
+    if (n_points < 1) return fail(MEEMB200_EINVAL, "n_points must be >= 1");
+    const double fr = reinterpret_cast<const double*>(P->blob.data() + h->off_freq)[f];
+    if (std::isinf(fr)) return fail(MEEMB200_EINVAL, "field evaluation needs a finite wavenumber");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    if (rc) return rc;
+    const long warps = (long)n_points;
+    const int blocks = (int)std::min<long>((warps + 7) / 8, (long)P->ctx->sm_count * 8);
+    k_fields<<<blocks, 256, 0, s>>>(d_in, d_ws, g, f, mode, d_X, (long)n_points, d_r, d_z, d_out);
     CUDA_TRY(cudaGetLastError());
     return MEEMB200_OK;
 }

@@ -158,6 +158,73 @@ class MEEMEngine:
                         "excitation_force": force, "c_vector": c[j]})
         return out
 
+    # ------------------------------------------------------------------ fields
+    @staticmethod
+    def make_R_Z(a, h, d, sharp, spatial_res, R_range=None, Z_range=None):
+        """Evaluation grid of the reference (multi_equations.py:478-501): host-side bookkeeping."""
+        a = np.asarray(a, dtype=float)
+        d = np.asarray(d, dtype=float)
+        if R_range is not None:
+            r_vec = np.asarray(R_range, dtype=float)
+        else:
+            rmin = (2 * a[-1] / spatial_res) if sharp else 0.0
+            r_vec = np.linspace(rmin, 2 * a[-1], spatial_res)
+        z_vec = np.asarray(Z_range, dtype=float) if Z_range is not None else np.linspace(0, -h, spatial_res)
+        if sharp:
+            a_eps = 1.0e-4
+            for i in range(len(a)):
+                r_vec = np.append(r_vec, a[i] * (1 - a_eps))
+                r_vec = np.append(r_vec, a[i] * (1 + a_eps))
+            r_vec = np.unique(r_vec)
+            for i in range(len(d)):
+                z_vec = np.append(z_vec, -d[i])
+            z_vec = np.unique(z_vec)
+        return np.meshgrid(r_vec, z_vec, indexing="ij")
+
+    def _raw_fields(self, problem, solution_vector, m0, R, Z):
+        geo = flatten_problem(problem, from_domain_flags=True)
+        # the particular solution follows the BODIES' heaving flags (meem_engine.py:405-407), per region
+        geo.mode_flags = np.asarray([[1 if x else 0 for x in problem.geometry.body_arrangement.heaving]], dtype=np.uint8)
+        plan = BatchPlan([geo], [m0], freq_kind=FREQ_M0, device=self.device)
+        raw = plan.fields(solution_vector, R.ravel(), Z.ravel())
+        return geo, {k: v.reshape(R.shape) for k, v in raw.items()}
+
+    def calculate_potentials(self, problem, solution_vector, m0, spatial_res, sharp, R_range=None, Z_range=None):
+        """phiH, phiP, phi on the reference's (R, Z) grid (meem_engine.py:395-467); arithmetic on the device, the
+        region / inside-the-body masks applied here exactly as the reference does."""
+        self._ensure_m_k_and_N_k_arrays(problem, m0)
+        ba = problem.geometry.body_arrangement
+        a, d, h = np.asarray(ba.a, float), np.asarray(ba.d, float), problem.geometry.h
+        R, Z = self.make_R_Z(a, h, d, sharp, spatial_res)          # the reference ignores R_range / Z_range here
+        _, raw = self._raw_fields(problem, solution_vector, m0, R, Z)
+        M = len(a)
+        inside = np.zeros(R.shape, dtype=bool)
+        inside |= (R <= a[0]) & ~(Z < -d[0])
+        for i in range(1, M):
+            inside |= (R > a[i - 1]) & (R <= a[i]) & ~(Z < -d[i])
+        nanc = np.nan + 1j * np.nan
+        phiH = np.where(inside, nanc, raw["phiH"])
+        phiP = np.where(inside, nanc, raw["phiP"].astype(complex))
+        return {"R": R, "Z": Z, "phiH": phiH, "phiP": phiP, "phi": phiH + phiP}
+
+    def calculate_velocities(self, problem, solution_vector, m0, spatial_res, sharp, R_range=None, Z_range=None):
+        """vrH, vzH, vrP, vzP, vr, vz (meem_engine.py:478-553)."""
+        self._ensure_m_k_and_N_k_arrays(problem, m0)
+        ba = problem.geometry.body_arrangement
+        a, d, h = np.asarray(ba.a, float), np.asarray(ba.d, float), problem.geometry.h
+        R, Z = self.make_R_Z(a, h, d, sharp, spatial_res, R_range=R_range, Z_range=Z_range)
+        _, raw = self._raw_fields(problem, solution_vector, m0, R, Z)
+        vrH, vzH = raw["vrH"], raw["vzH"]
+        vrP, vzP = raw["vrP"].astype(complex), raw["vzP"].astype(complex)
+        vr, vz = vrH + vrP, vzH + vzP
+        M = len(a)
+        for i in range(M):
+            reg = (R <= a[0]) if i == 0 else ((R > a[i - 1]) & (R <= a[i]))
+            body = reg & (Z > -d[i])
+            vr[body] = np.nan
+            vz[body] = np.nan
+        return {"R": R, "Z": Z, "vrH": vrH, "vzH": vzH, "vrP": vrP, "vzP": vzP, "vr": vr, "vz": vz}
+
     # ------------------------------------------------------------------ the hot path
     def run_and_store_results(self, problem_index: int) -> Results:
         """Frequency x mode sweep of one problem (meem_engine.py:555-690) in ONE device batch."""

@@ -591,3 +591,135 @@ def run_sweep(geo: FlatGeometry, omegas, region_body, modes, rho=RHO, want_X=Fal
     if want_X:
         out["X"] = X_all
     return out
+
+
+# --------------------------------------------------------------------------- fields
+def make_R_Z(a, h, d, sharp, spatial_res, R_range=None, Z_range=None):
+    """multi_equations.py:478-501."""
+    a = np.asarray(a, dtype=float)
+    d = np.asarray(d, dtype=float)
+    if R_range is not None:
+        r_vec = np.asarray(R_range, dtype=float)
+    else:
+        rmin = (2 * a[-1] / spatial_res) if sharp else 0.0
+        r_vec = np.linspace(rmin, 2 * a[-1], spatial_res)
+    z_vec = np.asarray(Z_range, dtype=float) if Z_range is not None else np.linspace(0, -h, spatial_res)
+    if sharp:
+        a_eps = 1.0e-4
+        for i in range(len(a)):
+            r_vec = np.append(r_vec, a[i] * (1 - a_eps))
+            r_vec = np.append(r_vec, a[i] * (1 + a_eps))
+        r_vec = np.unique(r_vec)
+        for i in range(len(d)):
+            z_vec = np.append(z_vec, -d[i])
+        z_vec = np.unique(z_vec)
+    return np.meshgrid(r_vec, z_vec, indexing="ij")
+
+
+def _Z_n_i(n, z, i, geo):
+    """multi_equations.py:301-308."""
+    n = np.asarray(n, dtype=float)
+    lam = np.where(n == 0, 0.0, lambda_ni(n, i, geo.h, geo.dext))
+    return np.where(n == 0, 1.0, np.sqrt(2) * np.cos(lam * (z + geo.h)))
+
+
+def _diff_Z_n_i(n, z, i, geo):
+    """multi_equations.py:310-318."""
+    n = np.asarray(n, dtype=float)
+    lam = np.where(n == 0, 0.0, lambda_ni(n, i, geo.h, geo.dext))
+    return np.where(n == 0, 0.0, -lam * np.sqrt(2) * np.sin(lam * (z + geo.h)))
+
+
+def _Lambda_k(k, r, m0, geo, mk, diff=False):
+    """multi_equations.py:322-374 (finite m0)."""
+    k = np.asarray(k)
+    aM = geo.a[-1]
+    safe = np.where(k == 0, 1.0, mk[k])
+    with np.errstate(all="ignore"):
+        if diff:
+            zero = -(m0 * hankel1(1, m0 * r)) / hankel1(0, m0 * aM)
+            non = ((-(safe * kve(1, safe * r))) / kve(0, safe * aM)) * np.exp(safe * (aM - r))
+            return np.where(k == 0, zero, non)
+        zero = hankel1(0, m0 * r) / hankel1(0, m0 * aM)
+        non = (kve(0, safe * r) / kve(0, safe * aM)) * np.exp(safe * (aM - r))
+    return np.where(r == aM, 1.0, np.where(k == 0, zero, non))
+
+
+def _Z_k_e(k, z, m0, h, mk, Nk, diff=False):
+    """multi_equations.py:388-416."""
+    k = np.asarray(k)
+    if not diff:
+        non = (1 / np.sqrt(Nk[k])) * np.cos(mk[k] * (z + h))
+        if m0 * h < M0_H_THRESH:
+            zero = (1 / np.sqrt(Nk[0])) * np.cosh(m0 * (z + h))
+        else:
+            zero = np.sqrt(2 * m0 * h) * (np.exp(m0 * z) + np.exp(-m0 * (z + 2 * h)))
+    else:
+        non = -(1 / np.sqrt(Nk[k])) * mk[k] * np.sin(mk[k] * (z + h))
+        if m0 * h < M0_H_THRESH:
+            zero = (1 / np.sqrt(Nk[0])) * m0 * np.sinh(m0 * (z + h))
+        else:
+            zero = m0 * np.sqrt(2 * h * m0) * (np.exp(m0 * z) - np.exp(-m0 * (z + 2 * h)))
+    return np.where(k == 0, zero, non)
+
+
+def fields(geo: FlatGeometry, X, m0, heaving, R, Z):
+    """Potential and velocity fields at the points (R, Z) (any shape): MEEMEngine.calculate_potentials
+    (meem_engine.py:395-467) and calculate_velocities (:478-553) with the reference's masks.
+    `heaving` = per-region flags.  Returns dict(phiH, phiP, phi, vrH, vzH, vrP, vzP, vr, vz)."""
+    h, a, d, NMK, M = geo.h, geo.a, geo.d, geo.NMK, geo.M
+    mk = m_k_array(NMK[-1], m0, h)
+    Nk = N_k_array(m0, h, mk)
+    R = np.asarray(R, dtype=float)
+    Z = np.asarray(Z, dtype=float)
+    Cs, col = [], 0
+    for i in range(M + 1):
+        w = NMK[i] if i in (0, M) else 2 * NMK[i]
+        Cs.append(np.asarray(X)[col:col + w])
+        col += w
+    rad = [R <= a[0]] + [(R > a[i - 1]) & (R <= a[i]) for i in range(1, M)] + [R > a[-1]]
+    nanc = np.nan + 1j * np.nan
+    phiH = np.full(R.shape, nanc, dtype=complex)
+    phiP = np.full(R.shape, nanc, dtype=complex)
+    vrH = np.full(R.shape, np.nan, dtype=complex)
+    vzH = np.full(R.shape, np.nan, dtype=complex)
+    vrP = np.zeros(R.shape, dtype=complex)
+    vzP = np.zeros(R.shape, dtype=complex)
+    for i in range(M + 1):
+        reg = rad[i]
+        if not np.any(reg):
+            continue
+        r, z = R[reg][None, :], Z[reg][None, :]
+        n = np.arange(NMK[i])[:, None]
+        if i == M:
+            c = Cs[i][:, None]
+            pH = np.sum(c * _Lambda_k(n, r, m0, geo, mk) * _Z_k_e(n, z, m0, h, mk, Nk), axis=0)
+            vr = np.sum(c * _Lambda_k(n, r, m0, geo, mk, diff=True) * _Z_k_e(n, z, m0, h, mk, Nk), axis=0)
+            vz = np.sum(c * _Lambda_k(n, r, m0, geo, mk) * _Z_k_e(n, z, m0, h, mk, Nk, diff=True), axis=0)
+            pP = np.zeros_like(pH)
+            pmask = np.ones(r.shape[1], dtype=bool)
+        else:
+            c1 = Cs[i][:NMK[i], None]
+            t, dt = c1 * R_1n(n, r, i, geo), c1 * diff_R_1n(n, r, i, geo)
+            if i > 0:
+                c2 = Cs[i][NMK[i]:, None]
+                t, dt = t + c2 * R_2n(n, r, i, geo), dt + c2 * diff_R_2n(n, r, i, geo)
+            pH = np.sum(t * _Z_n_i(n, z, i, geo), axis=0)
+            vr = np.sum(dt * _Z_n_i(n, z, i, geo), axis=0)
+            vz = np.sum(t * _diff_Z_n_i(n, z, i, geo), axis=0)
+            pP = heaving[i] * ((1 / (2 * (h - d[i]))) * ((z[0] + h) ** 2 - (r[0] ** 2) / 2))      # me.py:179-180
+            if heaving[i]:
+                vrP[reg] = heaving[i] * (-r[0] / (2 * (h - d[i])))                                # me.py:182-183
+                vzP[reg] = heaving[i] * ((z[0] + h) / (h - d[i]))                                 # me.py:185-186
+            pmask = z[0] < -d[i]
+        idx = np.where(reg)
+        sel = tuple(ix[pmask] for ix in idx)
+        phiH[sel] = pH[pmask]
+        phiP[sel] = pP[pmask]
+        vrH[reg], vzH[reg] = vr, vz
+    vr_t, vz_t = vrH + vrP, vzH + vzP
+    for i in range(M):
+        body = rad[i] & (Z > -d[i])
+        vr_t[body] = np.nan
+        vz_t[body] = np.nan
+    return dict(phiH=phiH, phiP=phiP, phi=phiH + phiP, vrH=vrH, vzH=vzH, vrP=vrP, vzP=vzP, vr=vr_t, vz=vz_t)

@@ -106,3 +106,57 @@ def test_plan_rejects_bad_geometry():
         ofb.BatchPlan([ofb.FlatGeometry(1.0, [0.5], [1.2], [3, 3])], [1.0])
     with pytest.raises(ValueError):
         ofb.BatchPlan([ofb.FlatGeometry(1.0, [0.5], [0.2], [3, 3])], [-1.0])
+
+
+ZF, METAF = load_npz("ref_fields.npz")
+
+
+@pytest.mark.parametrize("name", sorted(METAF))
+def test_fields_vs_reference_golden(name):
+    """MEEMEngine.calculate_potentials / calculate_velocities (device kernel k_fields through meemb200_fields) against
+    the untouched reference's outputs for the reference's own solution vector: same grid, same NaN masks, values
+    within 1e-11 of the field's scale (different summation order over the harmonics)."""
+    import openflash_b200 as ofb
+    c = METAF[name]
+    nb = max(c["body_map"]) + 1
+    prob = _problem(ofb, c, [False] * nb)
+    for bi, body in enumerate(prob.geometry.body_arrangement.bodies):
+        body.heaving = bool(c["heaving_bodies"][bi])
+    eng = ofb.MEEMEngine([prob])
+    X = ZF[name + "/X"]
+    pot = eng.calculate_potentials(prob, X, c["m0"], c["res"], c["sharp"])
+    vel = eng.calculate_velocities(prob, X, c["m0"], c["res"], c["sharp"])
+    assert np.array_equal(pot["R"], ZF[name + "/R"]) and np.array_equal(pot["Z"], ZF[name + "/Z"])
+    for src, keys in ((pot, ("phiH", "phiP", "phi")), (vel, ("vrH", "vzH", "vrP", "vzP", "vr", "vz"))):
+        for k in keys:
+            ref, got = ZF[f"{name}/{k}"], src[k]
+            assert np.array_equal(np.isnan(ref), np.isnan(got)), (name, k)
+            ok = ~np.isnan(ref)
+            scale = max(np.max(np.abs(ref[ok])), 1e-300)
+            assert np.max(np.abs(got[ok] - ref[ok])) <= 1e-11 * scale, (name, k, np.max(np.abs(got[ok] - ref[ok])) / scale)
+
+
+def test_fields_of_device_solution_vs_oracle():
+    """End to end on the device: solve on the GPU, evaluate the fields of that X on the GPU, compare with the oracle's
+    fields of the oracle's X (tolerance of X itself: 1e-9 of the field scale)."""
+    import openflash_b200 as ofb
+    from oracle import meem_oracle as mo
+    h, a, d, NMK = 20.0, [5.0, 10.0, 15.0], [15.0, 10.0, 5.0], [20] * 4
+    m0 = 0.35
+    flags = [1, 1, 0]
+    og = mo.FlatGeometry(h, a, d, NMK)
+    Xo = mo.solve_single(og, flags, m0)
+    rng = np.random.default_rng(5)
+    r = np.concatenate([rng.uniform(0.0, 30.0, 500), np.asarray(a), [0.0]])
+    z = np.concatenate([rng.uniform(-h, 0.0, 500), [-16.0, -12.0, -7.0], [-18.0]])
+    fo = mo.fields(og, Xo, m0, flags, r, z)
+    geo = ofb.FlatGeometry(h, a, d, NMK, [flags])
+    plan = ofb.BatchPlan([geo], [m0], freq_kind=ofb.FREQ_M0, want_x=True)
+    Xd = plan.run()[0]["X"][0, 0]
+    raw = plan.fields(Xd, r, z)
+    for k in ("vrH", "vzH"):
+        scale = np.max(np.abs(fo[k]))
+        assert np.max(np.abs(raw[k] - fo[k])) <= 1e-9 * scale, k
+    ok = ~np.isnan(fo["phiH"])
+    assert np.max(np.abs(raw["phiH"][ok] - fo["phiH"][ok])) <= 1e-9 * np.max(np.abs(fo["phiH"][ok]))
+    assert np.max(np.abs(raw["phiP"][ok] - fo["phiP"][ok].real)) <= 1e-13 * np.max(np.abs(fo["phiP"][ok]))

@@ -188,3 +188,51 @@ def test_cooperative_large_system_vs_oracle(ofb):
     res = ofb.solve_batch([geo], om)[0]
     assert np.all(res["status"] == 0)
     _check(res, ref)
+
+
+def test_big_tricylinder_full_size(ofb):
+    """BASELINE.json configs[2] at full size (N_T = 1200, 200 modes/region): the product path (cooperative LU,
+    DMMA GEMMs, Cholesky) against the oracle at three frequencies, and against the independent reference-shaped
+    dense complex LU on the device over a sweep that crosses the m0 h = 14 branch."""
+    h, a, d, NMK = 25.0, [10, 15, 20], [20, 15, 10], [200] * 4
+    og = mo.FlatGeometry(h, a, d, NMK)
+    om_o = [0.1, 1.37, 3.0]
+    ref = mo.run_sweep(og, om_o, [0, 0, 0], [0])
+    geo = ofb.FlatGeometry.from_body_map(h, a, d, NMK, [0, 0, 0], [0])
+    res = ofb.solve_batch([geo], om_o)[0]
+    assert np.all(res["status"] == 0)
+    _check(res, ref)
+    om = np.linspace(0.1, 3.0, 24)
+    r_s = ofb.solve_batch([geo], om, algo=ofb.ALGO_SCHUR)[0]
+    r_d = ofb.solve_batch([geo], om, algo=ofb.ALGO_DENSE)[0]
+    assert np.all(r_s["status"] == 0) and np.all(r_d["status"] == 0)
+    _check(r_s, r_d)
+
+
+def test_sweep_is_independent_of_batching(ofb):
+    """Size-independent property: a system's result does not depend on what else is in the batch (work queues,
+    cost sorting, waves): every frequency of a 4096-point sweep solved alone in small batches reproduces the
+    big batch bit for bit (same kernels, same operation order)."""
+    geo = ofb.FlatGeometry.from_body_map(20.0, [5, 10, 15], [15, 10, 5], [50] * 4, [0, 1, 1], [0, 1])
+    om = np.linspace(0.1, 3.0, 4096)
+    full = ofb.solve_batch([geo], om)[0]
+    assert np.all(full["status"] == 0)
+    idx = np.array([0, 1, 777, 2048, 4095])
+    part = ofb.solve_batch([geo], om[idx])[0]
+    for v in ("added_mass", "damping", "excitation_force", "excitation_phase"):
+        assert np.array_equal(full[v][idx], part[v]), v
+    # physics sanity over the whole sweep: radiation damping is positive and the 2 x 2 added mass is finite
+    assert np.all(np.diagonal(full["damping"], axis1=1, axis2=2) > 0)
+    assert np.isfinite(full["added_mass"]).all()
+
+
+def test_geometry_sweep_c4_vs_oracle(ofb):
+    """BASELINE.json configs[3] generator at its own mode count (16/region), first 12 geometries x 4 frequencies."""
+    import bench
+    gs = bench.c4_geometries(12)
+    om = np.linspace(0.3, 2.5, 4)
+    geos = [ofb.FlatGeometry.from_body_map(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"]) for g in gs]
+    res = ofb.solve_batch(geos, om)
+    for g, r in zip(gs, res):
+        og = mo.FlatGeometry(g["h"], g["a"], g["d"], g["NMK"])
+        _check(r, mo.run_sweep(og, om, g["body_map"], g["modes"]))
