@@ -6,9 +6,11 @@
 // the 2K^3/3 of a pivoted LU and no pivot search on the critical path.  A non-positive or non-finite
 // pivot raises a flag and the system is re-solved by the pivoted-LU kernel (k_freq_lu).
 //
-// The matrix lives row-major in the CTA's L2-resident slot (lower triangle, leading dimension ld, a
-// multiple of 8); `naug` extra rows below row K carry right-hand sides, so the forward substitution
-// L^{-1} r falls out of the panel solves.  Right-looking with panels of kCholNB = 16 columns:
+// The matrix is the PACKED lower triangle (row r holds columns 0..r, rows padded to an even length, tri_off(r)
+// doubles before it: 162 KB for K = 200), either in the system's L2-resident buffer or - when it fits - in shared
+// memory, where the whole factorisation then runs (k_freq_solve<.., true>).  `naug` extra full rows (leading
+// dimension lda) carry right-hand sides, so the forward substitution L^{-1} r falls out of the panel solves.
+// Right-looking with panels of kCholNB = 16 columns:
 //   diagonal block  one warp, in shared memory
 //   panel solve     one thread per row against the 16 x 16 factor (broadcast from shared memory)
 //   trailing update P22 -= L21 L21^T on the DMMA pipe, 32 x 32 warp tiles of the lower triangle,
@@ -21,12 +23,20 @@ namespace meem {
 constexpr int kCholNB = 16;
 constexpr int kCholLdP = kCholNB + 4;   // 20 = 4 (mod 16): conflict-free fragment loads
 
+// packed lower triangle: offset of row r (rows padded to even length so that double2 accesses stay aligned)
+__host__ __device__ inline int tri_off(int r) { const int h = r >> 1; return 2 * h * (h + 1) + ((r & 1) ? 2 * (h + 1) : 0); }
+__host__ __device__ inline int tri_doubles(int K) { return (tri_off(K) + 7) & ~7; }
+struct TriMat {
+    double* p;      // packed triangle
+    double* aug;    // augmented rows K.., row-major with leading dimension lda
+    int K, lda;
+    __device__ __forceinline__ double* row(int r) const { return r < K ? p + tri_off(r) : aug + (long)(r - K) * lda; }
+};
+
 __host__ __device__ inline size_t chol_smem_bytes(int K, int naug) {
     const int rows = ((K + naug + 31) / 32) * 32;
     return sizeof(double) * ((size_t)kCholNB * (kCholNB + 1) + kCholNB + (size_t)kCholNB * kCholLdP + (size_t)rows * kCholLdP);
 }
-// doubles of the per-system store of inverted diagonal blocks (used by the back-substitution)
-__host__ __device__ inline int chol_linv_doubles(int K) { return ((K + kCholNB - 1) / kCholNB) * kCholNB * kCholNB; }
 
 // Cholesky of one 16 x 16 diagonal block by one warp, rows in registers (lane i owns row i), then its inverse.
 // Dg (shared, [16][17]) holds the block on entry (identity-padded beyond nb); on exit Dg = L11 with the RECIPROCAL
@@ -38,18 +48,19 @@ __device__ __forceinline__ void warp_chol16(double* Dg, double* Li, int* fail) {
 #pragma unroll
     for (int c = 0; c < kCholNB; ++c) r[c] = Dg[row * (kCholNB + 1) + c];
     int bad = 0;
+    // right-looking, every update unconditional (entries above the diagonal hold garbage that is never read): keeps
+    // r[] in registers - a predicated update made the compiler spill the row to local memory
 #pragma unroll
     for (int j = 0; j < kCholNB; ++j) {
         const double d = __shfl_sync(0xffffffffu, r[j], j);
         if (!(d > 0.0) || d == INFINITY) bad |= (d == d && fabs(d) != INFINITY) ? 1 : 2;
         const double rinv = rsqrt(d);
         const double lij = r[j] * rinv;               // lane j: sqrt(d)
-        if (row == j) r[j] = rinv;                    // reciprocal diagonal
-        else r[j] = lij;
+        r[j] = (row == j) ? rinv : lij;               // reciprocal diagonal
 #pragma unroll
         for (int c = j + 1; c < kCholNB; ++c) {
             const double lcj = __shfl_sync(0xffffffffu, lij, c);
-            if (row >= c) r[c] = fma(-lij, lcj, r[c]);
+            r[c] = fma(-lij, lcj, r[c]);
         }
     }
     if (bad && lane == 0) atomicOr(fail, bad);
@@ -58,26 +69,36 @@ __device__ __forceinline__ void warp_chol16(double* Dg, double* Li, int* fail) {
         for (int c = 0; c < kCholNB; ++c) Dg[row * (kCholNB + 1) + c] = (c <= row) ? r[c] : 0.0;
     }
     __syncwarp();
-    // inverse: lane c solves L x = e_c  (x[i] = 0 for i < c)
-    if (lane < kCholNB) {
-        double x[kCholNB];
+    // inverse, column `row` per lane, right-looking so that the dependent chain is one multiply + one FMA per row:
+    // x_q = acc_q / L_qq, then acc_i -= L_iq x_q for every i > q
+    {
+        double acc[kCholNB];
 #pragma unroll
-        for (int i = 0; i < kCholNB; ++i) {
-            double acc = (i == lane) ? 1.0 : 0.0;
+        for (int i = 0; i < kCholNB; ++i) acc[i] = (i == row) ? 1.0 : 0.0;
 #pragma unroll
-            for (int q = 0; q < kCholNB; ++q)
-                if (q < i) acc = fma(-Dg[i * (kCholNB + 1) + q], x[q], acc);
-            x[i] = acc * Dg[i * (kCholNB + 1) + i];
+        for (int q = 0; q < kCholNB; ++q) {
+            const double xq = acc[q] * Dg[q * (kCholNB + 1) + q];
+            if (lane < kCholNB) Li[q * kCholLdP + row] = xq;                     // Linv[q][c]
+#pragma unroll
+            for (int i = q + 1; i < kCholNB; ++i) acc[i] = fma(-Dg[i * (kCholNB + 1) + q], xq, acc[i]);
         }
-#pragma unroll
-        for (int i = 0; i < kCholNB; ++i) Li[i * kCholLdP + lane] = x[i];       // Linv[i][c]
     }
 }
 
 // returns through *fail (shared int, OR-ed): bit 0 non-positive pivot, bit 1 non-finite pivot.
-// On exit the lower triangle of P holds L with the RECIPROCAL of its diagonal on the diagonal, rows K.. hold
-// (L^{-1} r_i)^T, and LI (global, chol_linv_doubles(K)) holds the inverses of the 16 x 16 diagonal blocks.
-__device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, double* sm, int* fail) {
+// On exit the strictly-below-block-diagonal part of P holds L, each 16 x 16 diagonal block holds the INVERSE of its
+// factor (lower triangular; its diagonal is 1 / L_ii) - the back-substitution only ever needs the inverse - and rows
+// K.. hold (L^{-1} r_i)^T.
+#ifdef MEEM_CHOL_PROF
+#define CHOL_T(i) do { const long long tn_ = clock64(); if (tsub) tsub[i] += tn_ - tprev_; tprev_ = tn_; } while (0)
+#else
+#define CHOL_T(i) do { } while (0)
+#endif
+__device__ void cta_cholesky(const TriMat P, int naug, double* sm, int* fail, long long* tsub = nullptr) {
+    const int K = P.K;
+#ifdef MEEM_CHOL_PROF
+    long long tprev_ = clock64();
+#endif
     double* Dg = sm;                                   // [16][17]
     double* Li = Dg + kCholNB * (kCholNB + 1) + kCholNB;   // [16][20] inverse of the current diagonal block
     double* Pn = Li + kCholNB * kCholLdP;              // [rows][20] current panel L21
@@ -91,16 +112,17 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
         __syncthreads();
         for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {
             const int i = idx >> 4, c = idx & 15;
-            Dg[i * (kCholNB + 1) + c] = (i < nb && c <= i) ? P[(long)(k0 + i) * ld + k0 + c] : (i == c ? 1.0 : 0.0);
+            Dg[i * (kCholNB + 1) + c] = (i < nb && c <= i) ? P.row(k0 + i)[k0 + c] : (i == c ? 1.0 : 0.0);
         }
         __syncthreads();
+        CHOL_T(0);
         if (warp == 0) warp_chol16(Dg, Li, fail);
         __syncthreads();
-        // factor block (reciprocal diagonal) back to the slot, inverse to the LI store
+        CHOL_T(1);
+        // the inverse of the factor block replaces the block
         for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {
             const int i = idx >> 4, c = idx & 15;
-            if (i < nb && c <= i) P[(long)(k0 + i) * ld + k0 + c] = Dg[i * (kCholNB + 1) + c];
-            LI[(long)(k0 / kCholNB) * kCholNB * kCholNB + idx] = Li[i * kCholLdP + c];
+            if (i < nb && c <= i) P.row(k0 + i)[k0 + c] = Li[i * kCholLdP + c];
         }
         const int nrow = KR - kb;
         if (nrow <= 0) break;
@@ -115,7 +137,7 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
                 for (int j = 0; j < 2; ++j) bf[ks][j] = Li[(8 * j + lr) * kCholLdP + ks * 4 + lc];   // b[k=q][n=c] = Linv[c][q]
             for (int rb = warp; rb < prow / 8; rb += nwarp) {
                 const int ri = rb * 8 + lr;
-                const double* src = P + (long)(kb + ri) * ld + k0;
+                double* src = P.row(kb + min(ri, nrow - 1)) + k0;
                 double af[kCholNB / 4];
 #pragma unroll
                 for (int ks = 0; ks < kCholNB / 4; ++ks) af[ks] = (ri < nrow && ks * 4 + lc < nb) ? src[ks * 4 + lc] : 0.0;
@@ -129,7 +151,7 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
                     const int col = 8 * j + 2 * lc;
                     *reinterpret_cast<double2*>(Pn + ri * kCholLdP + col) = make_double2(c[j][0], c[j][1]);
                     if (ri < nrow && col < nb) {
-                        double* dst = P + (long)(kb + ri) * ld + k0 + col;
+                        double* dst = src + col;
                         if (col + 1 < nb) *reinterpret_cast<double2*>(dst) = make_double2(c[j][0], c[j][1]);
                         else dst[0] = c[j][0];
                     }
@@ -137,6 +159,7 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
             }
         }
         __syncthreads();
+        CHOL_T(2);
         if (ncol <= 0) continue;
         // trailing update on the DMMA pipe: 16 x 32 warp tiles of the lower triangle, C tile is the accumulator
         const int ntr = prow / 16, ntc = (ncol + 31) / 32;
@@ -151,8 +174,8 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
                 for (int j = 0; j < 4; ++j) {
                     const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
                     double2 v = make_double2(0.0, 0.0);
-                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j))
-                        v = *reinterpret_cast<const double2*>(P + (long)(kb + r) * ld + kb + c);
+                    if (r < nrow && c <= r && c < ncol)
+                        v = *reinterpret_cast<const double2*>(P.row(kb + r) + kb + c);
                     acc[i][j][0] = v.x; acc[i][j][1] = v.y;
                 }
 #pragma unroll
@@ -172,10 +195,14 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
-                    if (r < nrow && c < ncol && (ri0 + 8 * i + 7 >= cj0 + 8 * j))
-                        *reinterpret_cast<double2*>(P + (long)(kb + r) * ld + kb + c) = make_double2(acc[i][j][0], acc[i][j][1]);
+                    if (r < nrow && c <= r && c < ncol)
+                        *reinterpret_cast<double2*>(P.row(kb + r) + kb + c) = make_double2(acc[i][j][0], acc[i][j][1]);
                 }
         }
+#ifdef MEEM_CHOL_PROF
+        __syncthreads();
+        CHOL_T(3);
+#endif
     }
     __syncthreads();
 }
@@ -183,13 +210,13 @@ __device__ void cta_cholesky(double* P, int ld, int K, int naug, double* LI, dou
 // Back-substitution L^T X = C for nrhs right-hand sides held as rows of X ([nrhs][ldx]).  Blocked bottom-up with
 // the inverted diagonal blocks: x_b = Linv_bb^T c_b is a 16 x 16 mat-vec (no serial chain), then the rows above
 // are updated.  nrhs <= 8 * blockDim.x / 16.
-__device__ void cta_chol_backsolve(const double* P, int ld, int K, const double* LI, double* X, int ldx, int nrhs) {
+__device__ void cta_chol_backsolve(const TriMat P, double* X, int ldx, int nrhs) {
     const int tid = threadIdx.x, nthr = blockDim.x;
+    const int K = P.K;
     const int nblk = (K + kCholNB - 1) / kCholNB;
     for (int blk = nblk - 1; blk >= 0; --blk) {
         const int k0 = blk * kCholNB;
         const int nb = min(kCholNB, K - k0);
-        const double* Lb = LI + (long)blk * kCholNB * kCholNB;
         __syncthreads();
         double xr[8];                                   // up to 8 passes of nthr / 16 right-hand sides
         const int c = tid & 15, rstep = nthr >> 4;
@@ -198,7 +225,7 @@ __device__ void cta_chol_backsolve(const double* P, int ld, int K, const double*
             const int r = (tid >> 4) + ps * rstep;
             double x = 0.0;
             if (r < nrhs && c < nb)
-                for (int q = c; q < nb; ++q) x = fma(Lb[q * kCholNB + c], X[(long)r * ldx + k0 + q], x);
+                for (int q = c; q < nb; ++q) x = fma(P.row(k0 + q)[k0 + c], X[(long)r * ldx + k0 + q], x);
             xr[ps] = x;
         }
         __syncthreads();
@@ -211,7 +238,7 @@ __device__ void cta_chol_backsolve(const double* P, int ld, int K, const double*
         for (int idx = tid; idx < nrhs * k0; idx += nthr) {
             const int rr = idx / k0, j = idx - rr * k0;
             double acc = X[(long)rr * ldx + j];
-            for (int q = 0; q < nb; ++q) acc = fma(-P[(long)(k0 + q) * ld + j], X[(long)rr * ldx + k0 + q], acc);
+            for (int q = 0; q < nb; ++q) acc = fma(-P.row(k0 + q)[j], X[(long)rr * ldx + k0 + q], acc);
             X[(long)rr * ldx + j] = acc;
         }
     }

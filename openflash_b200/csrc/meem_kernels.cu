@@ -726,15 +726,28 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
 // its latency only through many systems in flight per SM).
 // The exterior index k is stored permuted, kp = k - 1 (k >= 1), k = 0 -> kp = K - 1, so that the single complex
 // diagonal entry sits last and the leading K x K real part is what gets factorised.
-// gemm slot (doubles): Imk[N][ldk] | T[N][ldk];   system buffer: P[K+R+1][ldk] | qv[R][ldk] | xs[R+1][ldk] | misc[8] | LI[K/16][256]
+// gemm slot (doubles): Imk[N][ldk] | T[N][ldk]
+// system buffer: Ptri[tri_doubles(K)] (packed lower triangle) | aug[2R][ldk] (rows r_i, then q_j) | ext[ldk] | xs[R+1][ldk] | misc[8]
+// The q_j ride through the factorisation as right-hand sides like the r_i: with P = L L^T, q_j . P^{-1} r_i =
+// (L^{-1} q_j) . (L^{-1} r_i), and everything the coefficients need from z = P^{-1} e_last is L_KK and (L^{-1} q_j)_K -
+// so the coefficient path has no back-substitution at all (only the optional X output does).
 __host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * N * pad8(K) + 16; }
-__host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)(K + 3 * R + 2) * pad8(K) + 8 + chol_linv_doubles(K); }
-__host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N) {
-    return chol_smem_bytes(K, R) + sizeof(double) * (size_t)(2 * R * K + 2 * R * N);      // + xc, vv for the X path
+__host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)tri_doubles(K) + (int64_t)(3 * R + 2) * pad8(K) + 8; }
+// k_freq_solve dynamic shared memory: Cholesky scratch | xc, vv (X path) | [resident variant: Ptri | aug[R][ldk] | xs[R+1][ldk]]
+__host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N, bool want_x, bool resident) {
+    size_t b = chol_smem_bytes(K, 2 * R);
+    if (want_x) b += sizeof(double) * (size_t)(2 * R * K + 2 * R * N);
+    if (resident) b += sizeof(double) * ((size_t)tri_doubles(K) + (size_t)(3 * R + 1) * pad8(K));
+    return b;
 }
 
 enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, PH_COUNT };
 #define PHASE_END(ph) do { __syncthreads(); const long long tn_ = clock64(); tph[ph] += tn_ - tprev; tprev = tn_; } while (0)
+#ifdef MEEM_CHOL_PROF      // the solve kernel's four profile slots then carry the Cholesky's sub-phases instead
+#define PHASE_END_S(ph) __syncthreads()
+#else
+#define PHASE_END_S(ph) PHASE_END(ph)
+#endif
 
 __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws, int item0, int item1, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -765,15 +778,15 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         double* Imk = slot;
         double* T = Imk + (int64_t)N * ldk;
         double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
-        double* P = sys;
-        double* qv = P + (int64_t)(K + R + 1) * ldk;
-        double* misc = qv + (int64_t)(2 * R + 1) * ldk;
+        double* P = sys;                                   // packed lower triangle
+        double* aug = P + tri_doubles(K);                  // [2R][ldk] right-hand sides r_i, then q_j
+        double* ext = aug + (int64_t)2 * R * ldk;          // 1. exterior diagonal (real parts)
+        double* misc = ext + (int64_t)(R + 2) * ldk;
         const double* gs = v.gstore + gd.gs_off;
         const double* HT = gs;
         const double* wv = HT + (int64_t)N * ldn;
         const double* uv = wv + (int64_t)R * N;
-        // 1. coupling table (columns permuted) and exterior diagonal (real parts to the last row of P's block, +1)
-        double* ext = P + (int64_t)(K + R) * ldk;
+        // 1. coupling table (columns permuted)
         // Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
         //   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
         // with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
@@ -863,16 +876,16 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         cta_gemm_dmma(HT, ldn, Imk, ldk, N + 2 * R, K, N, false, sm, [&](int m, int n, double v0, double v1) {
             if (n >= K) return;
             if (m < N) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
-            else if (m < N + R) *reinterpret_cast<double2*>(P + (long)(K + m - N) * ldk + n) = make_double2(-v0, -v1);
-            else if (m < N + 2 * R) *reinterpret_cast<double2*>(qv + (long)(m - N - R) * ldk + n) = make_double2(v0, v1);
+            else if (m < N + R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(-v0, -v1);
+            else if (m < N + 2 * R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(v0, v1);
         });
         PHASE_END(PH_GEMM1);
         // 4. P = Imk^T T - Re(D), lower triangle
         cta_gemm_dmma(Imk, ldk, T, ldk, K, K, N, true, sm, [&](int m, int n, double v0, double v1) {
-            if (m < K && n < K) {
+            if (m < K && n <= m) {
                 if (m == n) v0 -= ext[m];
                 if (m == n + 1) v1 -= ext[m];
-                *reinterpret_cast<double2*>(P + (long)m * ldk + n) = make_double2(v0, v1);
+                *reinterpret_cast<double2*>(P + tri_off(m) + n) = make_double2(v0, v1);
             }
         });
         PHASE_END(PH_GEMM2);
@@ -883,12 +896,33 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
     }
 }
 
-__global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
+// mbarrier + 1-D bulk copy (TMA unit, SASS UBLKCP) used to bring a system's packed P into shared memory
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+
+// RESIDENT: the packed P (+ right-hand-side rows) is pulled into shared memory with one bulk copy and the whole
+// factorisation / back-substitution runs there (K <= ~208 at one CTA per SM); otherwise P stays in its L2-resident buffer.
+template <int THREADS, int MINB, bool RESIDENT>
+__global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
     __shared__ int sh_item, sh_fail;
     __shared__ double sh_dots[64];
+    __shared__ __align__(8) uint64_t sh_bar;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -896,6 +930,12 @@ __global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* w
     const int F = v.hdr->n_freq;
     long long tph[4] = {0, 0, 0, 0};
     long long tprev = clock64();
+    unsigned bar_phase = 0;
+    if (RESIDENT) {
+        if (tid == 0) mbar_init(&sh_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        __syncthreads();
+    }
     for (;;) {
         const int item = item0 + next_item(counter, &sh_item);
         if (item >= item1) break;
@@ -904,38 +944,62 @@ __global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* w
         const Geom g = geom_of(v, gd);
         const RootSet rs = v.sets[gd.root_set];
         const double m0 = v.roots[rs.off + f];
-        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_fail = 0; }
-        __syncthreads();
         const int N = gd.N, K = gd.K, R = gd.R, M = gd.M, p = gd.p;
         const int ldk = pad8(K), ldn = gs_ldn(N, R);
         double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
-        double* P = sys;
-        double* qv = P + (int64_t)(K + R + 1) * ldk;
-        double* xs = qv + (int64_t)R * ldk;
-        const double* misc = xs + (int64_t)(R + 1) * ldk;
+        double* xsg = sys + tri_doubles(K) + (int64_t)(2 * R + 1) * ldk;
+        const double* misc = xsg + (int64_t)(R + 1) * ldk;
+        double* xpath = sm + chol_smem_bytes(K, 2 * R) / sizeof(double);      // xc, vv (X path only)
+        double* res = xpath + (out.x != nullptr ? 2 * R * K + 2 * R * N : 0);  // resident copy of Ptri | aug
+        TriMat P;
+        P.K = K; P.lda = ldk;
+        P.p = RESIDENT ? res : sys;
+        P.aug = P.p + tri_doubles(K);
+        double* xs = RESIDENT ? P.aug + (int64_t)2 * R * ldk : xsg;
+        if (RESIDENT && tid == 0) {
+            // the previous system's generic-proxy accesses to this shared memory were ordered by next_item's barriers
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            const unsigned bytes = 8u * (unsigned)(tri_doubles(K) + 2 * R * ldk);
+            mbar_expect_tx(&sh_bar, bytes);
+            for (unsigned o = 0; o < bytes; o += 32768u)
+                bulk_g2s(reinterpret_cast<char*>(res) + o, reinterpret_cast<const char*>(sys) + o, min(32768u, bytes - o), &sh_bar);
+        }
+        if (tid == 0) { make_layout(g, L); make_exterior(g, m0, ex); sh_fail = 0; }
         const double* gs = v.gstore + gd.gs_off;
         const double* s0 = gs + (int64_t)N * ldn + 2LL * R * N;
         const double* phi = s0 + R * R;
         const double* bc = phi + R;
         const int gstatus = (int)bc[R];
-        // 5. P = L L^T; rows K.. become L^{-1} r_i
-        double* LI = xs + (int64_t)(R + 1) * ldk + 8;
-        cta_cholesky(P, ldk, K, R, LI, sm, &sh_fail);
+        if (RESIDENT) { mbar_wait(&sh_bar, bar_phase); bar_phase ^= 1u; }
+        __syncthreads();
+        // 5. P = L L^T; rows K.. become L^{-1} r_i and L^{-1} q_j
+#ifdef MEEM_CHOL_PROF
+        cta_cholesky(P, 2 * R, sm, &sh_fail, tph);
+        tprev = clock64();
+#else
+        cta_cholesky(P, 2 * R, sm, &sh_fail);
         PHASE_END(0);
-        // 6. back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last  (the diagonal of P holds 1 / L_ii)
-        for (int t = tid; t < (R + 1) * K; t += nthr) {
-            const int r = t / K, kp = t - r * K;
-            xs[(long)r * ldk + kp] = (r < R) ? P[(long)(K + r) * ldk + kp]
-                                             : (kp == K - 1 ? P[(long)(K - 1) * ldk + K - 1] : 0.0);
+#endif
+        // 6. (X output only) back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last.  The diagonal blocks of P hold the
+        // inverses of the factor's diagonal blocks, so P[K-1][K-1] = 1 / L_KK is the forward-solved e_last.
+        const double* fr = P.aug;                          // (L^{-1} r_i)^T
+        const double* fq = P.aug + (int64_t)R * ldk;       // (L^{-1} q_j)^T
+        const double linv_last = P.row(K - 1)[K - 1];
+        if (out.x != nullptr) {
+            for (int t = tid; t < (R + 1) * K; t += nthr) {
+                const int r = t / K, kp = t - r * K;
+                xs[(long)r * ldk + kp] = (r < R) ? fr[(long)r * ldk + kp] : (kp == K - 1 ? linv_last : 0.0);
+            }
+            cta_chol_backsolve(P, xs, ldk, R + 1);
         }
-        cta_chol_backsolve(P, ldk, K, LI, xs, ldk, R + 1);
-        PHASE_END(1);
-        // 7. coefficients (eng.py:370-391).  x2_i = w_i + i beta x_e z,  x_e = w_e / (1 - i beta z_e)
+        PHASE_END_S(1);
+        // 7. coefficients (eng.py:370-391).  x2_i = w_i + i beta x_e z,  x_e = w_e / (1 - i beta z_e), with
+        // q_j . w_i = fq_j . fr_i,  q_j . z = fq_j[K-1] / L_KK,  w_e = fr_i[K-1] / L_KK,  z_e = 1 / L_KK^2
         const double beta = misc[0];
         const double* zv = xs + (long)R * ldk;
-        for (int t = warp; t < R * R + R; t += nwarp) {     // q_j . w_i  and  q_j . z
-            const double* qa = qv + (long)((t < R * R) ? t / R : t - R * R) * ldk;
-            const double* xb = (t < R * R) ? xs + (long)(t % R) * ldk : zv;
+        for (int t = warp; t < R * R; t += nwarp) {
+            const double* qa = fq + (long)(t / R) * ldk;
+            const double* xb = fr + (long)(t % R) * ldk;
             double a = 0.0;
             for (int k = lane; k < K; k += 32) a = fma(qa[k], xb[k], a);
             a = warp_sum(a);
@@ -946,20 +1010,18 @@ __global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* w
         const int status = gstatus | (fail ? 4 : 0);
         const int64_t sysi = gd.out_sys + f;
         if (tid == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
-        const double ze = zv[K - 1];
+        const double ze = linv_last * linv_last;
         const double den = 1.0 + beta * beta * ze * ze;
         for (int t = tid; t < R * R; t += nthr) {
             const int j = t / R, i = t - j * R;
-            const double we = xs[(long)i * ldk + K - 1];
+            const double we = fr[(long)i * ldk + K - 1] * linv_last;
             const double xer = we / den, xei = we * beta * ze / den;      // x_e = we (1 + i beta ze) / den
-            double qw, qz;
-            if (R * R + R <= 64) { qw = sh_dots[t]; qz = sh_dots[R * R + j]; }
+            const double qz = fq[(long)j * ldk + K - 1] * linv_last;
+            double qw;
+            if (R * R <= 64) qw = sh_dots[t];
             else {   // many modes: recompute serially (rare)
-                qw = 0.0; qz = 0.0;
-                for (int k = 0; k < K; ++k) {
-                    qw = fma(qv[(long)j * ldk + k], xs[(long)i * ldk + k], qw);
-                    qz = fma(qv[(long)j * ldk + k], zv[k], qz);
-                }
+                qw = 0.0;
+                for (int k = 0; k < K; ++k) qw = fma(fq[(long)j * ldk + k], fr[(long)i * ldk + k], qw);
             }
             const double cre = 2.0 * kPi * ((s0[j * R + i] + (qw - beta * xei * qz)) + phi[j]);
             const double cim = 2.0 * kPi * (beta * xer * qz);
@@ -978,12 +1040,12 @@ __global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* w
                 out.phase[o1] = ph;
             }
         }
-        PHASE_END(2);
+        PHASE_END_S(2);
         // 8. optional X = [y0 + G v ; x2],  v = Imk x2 (Imk entries recomputed: the gemm kernel's slot is gone)
         if (out.x != nullptr && gd.xg_off >= 0) {
             const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
             const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
-            double* xc = sm + chol_smem_bytes(K, R) / sizeof(double);     // x2_i[k] complex, natural k order
+            double* xc = xpath;                                            // x2_i[k] complex, natural k order
             double* vv = xc + 2 * R * K;                                  // v_i[n] complex
             for (int e = tid; e < R * K; e += nthr) {
                 const int i = e / K, kp = e - i * K;
@@ -1035,7 +1097,7 @@ __global__ void __launch_bounds__(128, 5) k_freq_solve(const void* blob, void* w
                 xo[0] = status ? NAN : xc[2 * e];
                 xo[1] = status ? NAN : xc[2 * e + 1];
             }
-            PHASE_END(3);
+            PHASE_END_S(3);
         }
     }
     if (tid == 0) {
@@ -1356,6 +1418,7 @@ struct meemb200_plan {
     bool use_coop;          // grid-cooperative geometry stage (few large geometries)
     int64_t wave_items;     // systems per frequency-stage wave
     int n_waves, solve_grid;
+    int solve_variant;      // k_freq_solve: 0 = P in its L2-resident buffer (128 threads), 1/2/3 = P resident in shared memory, 128/256/512 threads
     int max_tab_threads;
     int64_t max_FK;
     cudaEvent_t ev[6];      // 0 start, 1 after roots, 2 after geometry, 3 after last k_freq_gemm, 4 after last k_freq_solve, 5 end
@@ -1499,7 +1562,18 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->algo = b->algo;
     int max_R = 1;
     for (int gi = 0; gi < G; ++gi) max_R = std::max(max_R, P->geoms[gi].R);
-    P->smem_chol = b->want_x ? freq2_solve_smem_bytes(max_K, max_R, max_N) : chol_smem_bytes(max_K, max_R);
+    // k_freq_solve variant: P resident in shared memory when it fits (2 KB reserved for the kernel's static shared memory)
+    P->smem_chol = freq2_solve_smem_bytes(max_K, max_R, max_N, b->want_x, true);
+    // Resident by default only while >= 5 CTAs still fit an SM (K <~ 75): the factorisation is a latency chain (13 panels
+    // at K = 200, each with a 16-step register Cholesky) that is hidden by CTAs in flight, not by threads per CTA -
+    // measured on big_tricylinder: L2-resident 5 CTAs/SM 2.9 ms, shared-memory-resident 1 CTA/SM x 512 threads 3.0 ms.
+    const bool fits = P->smem_chol + 2048 <= limit;
+    P->solve_variant = (fits && P->smem_chol <= 44 * 1024) ? 1 : 0;
+    if (const char* ev = getenv("MEEMB200_SOLVE_VARIANT")) {      // tuning / test override
+        const int want = atoi(ev);
+        if (want == 0 || (fits && want >= 1 && want <= 3)) P->solve_variant = want;
+    }
+    if (!P->solve_variant) P->smem_chol = freq2_solve_smem_bytes(max_K, max_R, max_N, b->want_x, false);
     if (schur && P->smem_chol > limit) { delete P; return fail(MEEMB200_EINVAL, "exterior mode count too large for the shared-memory Cholesky panel"); }
     if ((schur && (!P->nb_geom || !P->nb_freq)) || (b->algo == MEEMB200_ALGO_DENSE && !P->nb_dense)) {
         delete P;
@@ -1641,13 +1715,20 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
     if (P->algo == MEEMB200_ALGO_SCHUR) {
         e = cudaFuncSetAttribute(k_freq_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_freq_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_chol);
+        typedef void (*solve_fn)(const void*, void*, OutPtrs, int, int, int*);
+        static const solve_fn solve_k[4] = {k_freq_solve<128, 5, false>, k_freq_solve<128, 5, true>, k_freq_solve<256, 2, true>,
+                                            k_freq_solve<512, 1, true>};
+        static const int solve_thr[4] = {128, 128, 256, 512};
+        const solve_fn ksolve = solve_k[P->solve_variant];
+        const int nthr_solve = solve_thr[P->solve_variant];
+        e = cudaFuncSetAttribute(ksolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_chol);
         if (e != cudaSuccess) return e;
         if (!P->solve_grid) {
             int per_sm = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_freq_solve, 128, P->smem_chol);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ksolve, nthr_solve, P->smem_chol);
             if (e != cudaSuccess) return e;
-            P->solve_grid = std::max(1, per_sm) * P->ctx->sm_count;
+            if (per_sm < 1) return cudaErrorInvalidConfiguration;
+            P->solve_grid = per_sm * P->ctx->sm_count;
         }
         const BlobHeader* h = P->hdr();
         int* wave_counters = reinterpret_cast<int*>(static_cast<char*>(ws) + h->ws_counters + 256);
@@ -1657,7 +1738,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
             const int n = item1 - item0;
             k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[3], s);
-            k_freq_solve<<<std::min(n, P->solve_grid), 128, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
+            ksolve<<<std::min(n, P->solve_grid), nthr_solve, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[4], s);
         }
         e = cudaGetLastError();
