@@ -94,6 +94,8 @@ __device__ __forceinline__ void warp_chol16(double* Dg, double* Li, int* fail) {
 #else
 #define CHOL_T(i) do { } while (0)
 #endif
+// KEEP_FACTOR: the diagonal blocks keep the factor itself (with the reciprocal diagonal) instead of its inverse (k_hchol).
+template <bool KEEP_FACTOR = false>
 __device__ void cta_cholesky(const TriMat P, int naug, double* sm, int* fail, long long* tsub = nullptr) {
     const int K = P.K;
 #ifdef MEEM_CHOL_PROF
@@ -122,7 +124,7 @@ __device__ void cta_cholesky(const TriMat P, int naug, double* sm, int* fail, lo
         // the inverse of the factor block replaces the block
         for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {
             const int i = idx >> 4, c = idx & 15;
-            if (i < nb && c <= i) P.row(k0 + i)[k0 + c] = Li[i * kCholLdP + c];
+            if (i < nb && c <= i) P.row(k0 + i)[k0 + c] = KEEP_FACTOR ? Dg[i * (kCholNB + 1) + c] : Li[i * kCholLdP + c];
         }
         const int nrow = KR - kb;
         if (nrow <= 0) break;

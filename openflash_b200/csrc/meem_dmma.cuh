@@ -88,8 +88,10 @@ __device__ __forceinline__ void gemm_chunk(const double* As, const double* Bs, i
 }
 
 template <class Epi>
+// tri >= 0: A is "upper trapezoidal from column tri on" - A[k][m] = 0 for k < m - tri - so a tile whose first output row
+// is m0 starts its contraction at the chunk containing m0 - tri.
 __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const double* __restrict__ B, int ldb,
-                              int Mm, int Nn, int Kd, bool lower_only, double* sm, Epi epi) {
+                              int Mm, int Nn, int Kd, bool lower_only, int tri, double* sm, Epi epi) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int wr = warp >> 2, wc = warp & 3;            // 2 x 4 warps
     const int lr = lane >> 2, lc = lane & 3;
@@ -121,9 +123,10 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
 #pragma unroll
                 for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
             __syncthreads();      // previous users of the stage buffers are done
-            gemm_stage_load(sm, A, lda, B, ldb, m0, n0, Mlim, Nlim, 0, Kd);
+            const int c0 = (tri >= 0 && m0 > tri) ? (m0 - tri) / kGemmKC : 0;
+            gemm_stage_load(sm + (c0 & 1) * kGemmStageDoubles, A, lda, B, ldb, m0, n0, Mlim, Nlim, c0 * kGemmKC, Kd);
             cp_async_commit();
-            for (int c = 0; c < nchunk; ++c) {
+            for (int c = c0; c < nchunk; ++c) {
                 double* cur = sm + (c & 1) * kGemmStageDoubles;
                 if (c + 1 < nchunk) {
                     gemm_stage_load(sm + ((c + 1) & 1) * kGemmStageDoubles, A, lda, B, ldb, m0, n0, Mlim, Nlim,

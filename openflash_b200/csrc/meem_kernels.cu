@@ -116,8 +116,21 @@ __host__ __device__ inline int pad8(int n) { return (n + 7) & ~7; }
 // Columns N .. N+R-1 of HT hold u'_i = u_i + bc_i e_0 and columns N+R .. N+2R-1 hold w_j, so that the frequency
 // stage's T = H Imk GEMM also yields the right-hand sides and q_j = Imk^T w_j (rows N .. N+2R-1 of its output).
 __host__ __device__ inline int gs_ldn(int N, int R) { return pad8(N + 2 * R); }
-__host__ __device__ inline int64_t gs_doubles(int N, int R) {
+__host__ __device__ inline int64_t gs_base_doubles(int N, int R) {
     return (((int64_t)N * gs_ldn(N, R) + 2LL * R * N + (int64_t)R * R + 2 * R + 2) + 7) & ~7LL;
+}
+// ... followed by the factorised form of H (k_hchol): LA[N][ldn] | perm[N] (int32).  status is followed by hrank.
+// H is symmetric positive semidefinite (tools/experiments/exp_hchol.py): with its zero rows permuted to the end,
+// Pm^T H Pm = L L^T (L: N x hrank, lower trapezoidal) reproduces it to rounding.  Row k of LA belongs to harmonic
+// perm[k]: columns 0 .. 2R-1 = [u'_i | w_j] of that harmonic, columns 2R .. 2R+hrank-1 = L[k][:].  With it
+// P = Imk^T H Imk - Re D = W^T W - Re D, W = L^T (Pm^T Imk): a triangular product (half the flops of H Imk) followed by
+// a symmetric rank-N update.  hrank <= 0: factorisation not available (H not PSD to rounding, or N too large for the
+// shared-memory factor) and the frequency stage uses H itself.
+__host__ __device__ inline int64_t gs_doubles(int N, int R) {
+    return gs_base_doubles(N, R) + (int64_t)N * gs_ldn(N, R) + pad8((N + 1) / 2);
+}
+__host__ __device__ inline size_t hchol_smem_bytes(int N) {
+    return chol_smem_bytes(N, 0) + sizeof(double) * (size_t)tri_doubles(N) + sizeof(int) * (size_t)(N + 8);
 }
 
 struct OutPtrs {
@@ -467,6 +480,90 @@ struct GemmSmem {
     double Bs[16][64];
 };
 
+// ------------------------------------------------------------------------------------------------
+// Cholesky of H without its numerically zero rows (one CTA per geometry, packed triangle in shared memory, the same
+// blocked DMMA factorisation as the frequency systems); see gs_doubles.  The zero rows (structurally: harmonic 0, whose
+// radial derivative vanishes) go to the end of the permutation; the remaining block is well conditioned (smallest /
+// largest eigenvalue >= 4e-3 over every geometry probed), so no pivoting is needed.  Any non-positive pivot or negative
+// diagonal marks the geometry as not factorised and the frequency stage uses H itself.
+constexpr int kHcholThreads = 256;
+__global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void* ws, unsigned smem_limit) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red_v[kHcholThreads / 32];
+    __shared__ int sh_fail, sh_rank;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    for (int gi = blockIdx.x; gi < v.hdr->n_geom; gi += gridDim.x) {
+        const GeomDesc gd = v.geom[gi];
+        const int N = gd.N, R = gd.R, ldn = gs_ldn(N, R);
+        double* gs = v.gstore + gd.gs_off;
+        const double* HT = gs;
+        double* st = gs + (int64_t)N * ldn + 2LL * R * N + (int64_t)R * R + 2 * R;
+        double* LA = gs + gs_base_doubles(N, R);
+        int* permg = reinterpret_cast<int*>(LA + (int64_t)N * ldn);
+        __syncthreads();
+        if (hchol_smem_bytes(N) > smem_limit || st[0] != 0.0) {
+            if (tid == 0) st[1] = -1.0;
+            continue;
+        }
+        double* sm = reinterpret_cast<double*>(smem);
+        double* tri = sm + chol_smem_bytes(N, 0) / sizeof(double);
+        int* perm = reinterpret_cast<int*>(tri + tri_doubles(N));
+        // largest diagonal entry
+        double dmax = -INFINITY;
+        bool nan = false;
+        for (int i = tid; i < N; i += nthr) { const double x = HT[(int64_t)i * ldn + i]; dmax = fmax(dmax, x); nan |= !(x == x); }
+        if (nan) dmax = INFINITY;
+        for (int o = 16; o; o >>= 1) dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        if (lane == 0) red_v[warp] = dmax;
+        if (tid == 0) sh_fail = 0;
+        __syncthreads();
+        dmax = red_v[0];
+        for (int w = 1; w < nwarp; ++w) dmax = fmax(dmax, red_v[w]);
+        const double tol = 64.0 * (double)N * 2.220446049250313e-16 * dmax;
+        if (tid == 0) {
+            int nz = 0, bad = !(dmax > 0.0) || !(dmax < INFINITY);
+            for (int i = 0; i < N && !bad; ++i) {
+                const double x = HT[(int64_t)i * ldn + i];
+                if (x > tol) perm[nz++] = i;
+                else if (x < -tol) bad = 1;
+            }
+            if (!bad) {
+                int z = nz;
+                for (int i = 0; i < N; ++i) if (!(HT[(int64_t)i * ldn + i] > tol)) perm[z++] = i;
+            }
+            sh_rank = bad ? -1 : nz;
+        }
+        __syncthreads();
+        int rank = sh_rank;
+        if (rank > 0) {
+            for (int e = tid; e < rank * rank; e += nthr) {
+                const int r = e / rank, c = e - r * rank;
+                if (c <= r) tri[tri_off(r) + c] = HT[(int64_t)perm[r] * ldn + perm[c]];
+            }
+            TriMat P;
+            P.p = tri; P.aug = tri; P.K = rank; P.lda = 0;
+            __syncthreads();
+            cta_cholesky<true>(P, 0, sm, &sh_fail);
+            if (sh_fail) rank = -1;
+        }
+        if (tid == 0) {
+            st[1] = (double)rank;
+            if (rank > 0) atomicAdd(reinterpret_cast<unsigned long long*>(v.counters + 16) + 1, 1ULL);
+        }
+        if (rank > 0) {
+            for (int e = tid; e < N * ldn; e += nthr) {
+                const int k = e / ldn, c = e - k * ldn, m = c - 2 * R;
+                double val = 0.0;
+                if (c < 2 * R) val = HT[(int64_t)perm[k] * ldn + N + c];
+                else if (k < rank && m <= k) val = (m == k) ? 1.0 / tri[tri_off(k) + k] : tri[tri_off(k) + m];
+                LA[e] = val;
+            }
+            for (int i = tid; i < N; i += nthr) permg[i] = perm[i];
+        }
+    }
+}
+
 template <class Store>
 __device__ void cta_gemm_tn(const double* A, long lda, const double* B, long ldb, int Mm, int Nn, int Kd,
                             GemmSmem& sm, Store store) {
@@ -753,7 +850,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
-    __shared__ int sh_item;
+    __shared__ int sh_item, sh_row0;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -785,8 +882,13 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         const double* gs = v.gstore + gd.gs_off;
         const double* HT = gs;
         const double* wv = HT + (int64_t)N * ldn;
-        const double* uv = wv + (int64_t)R * N;
-        // 1. coupling table (columns permuted)
+        // factorised H (k_hchol): row kk of LA / of the coupling table belongs to harmonic perm[kk]
+        const int hrank = (int)gs[(int64_t)N * ldn + 2LL * R * N + (int64_t)R * R + 2 * R + 1];
+        const bool lmode = hrank > 0;
+        const double* LA = gs + gs_base_doubles(N, R);
+        const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
+#define HARM(kk) (lmode ? perm[kk] : (kk))
+        // 1. coupling table (columns permuted; rows permuted in the factorised-H form)
         // Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
         //   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
         // with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
@@ -813,7 +915,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
                 tnk[kp] = sqrt(2.0 / Nk[k]) * 0.5;
             }
             for (int n = tid; n < N; n += nthr) {
-                const double lam = lambda_ni(n, g.M - 1, g);
+                const double lam = lambda_ni(HARM(n), g.M - 1, g);
                 double sv, cv;
                 const double pr = lam * Lh, er = fma(lam, Lh, -pr);
                 sincos(pr, &sv, &cv);
@@ -821,16 +923,20 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
             }
             __syncthreads();
             // row m = 0 and column k = 0 (reference-ordered forms), kept out of the main loop so that it stays uniform
-            for (int e = tid; e < K + N - 1; e += nthr) {
-                const int n = (e < K) ? 0 : e - K + 1, kp = (e < K) ? e : K - 1;
-                Imk[(long)n * ldk + kp] = imk(n, (kp == K - 1) ? 0 : kp + 1, g, ex, mk, Nk);
+            for (int e = tid; e < N * 2; e += nthr) {                 // column k = 0 of every row; find the row of harmonic 0
+                const int kk = e >> 1;
+                if (e & 1) { if (HARM(kk) == 0) sh_row0 = kk; }
+                else Imk[(long)kk * ldk + K - 1] = imk(HARM(kk), 0, g, ex, mk, Nk);
             }
+            __syncthreads();
+            for (int kp = tid; kp < K - 1; kp += nthr) Imk[(long)sh_row0 * ldk + kp] = imk(0, kp + 1, g, ex, mk, Nk);
             // interior: one row per warp, lanes over the columns, branch-free except the exact-equality case.
             //   (a + b) / sp + S / sd  over the common denominator, S = sin(sd L):  a - b away from a resonance,
             //   x sinc(x) (Taylor, |x| = |sd L| < 1) near one, where a - b would lose digits to cancellation
             {
                 const int lane_ = tid & 31, warp_ = tid >> 5, nwarp_ = nthr >> 5;
-                for (int n = 1 + warp_; n < N; n += nwarp_) {
+                for (int n = warp_; n < N; n += nwarp_) {
+                    if (n == sh_row0) continue;
                     const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
                     double* row = Imk + (long)n * ldk;
                     for (int kp = lane_; kp < K - 1; kp += 32) {
@@ -861,7 +967,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
             for (int e = tid; e < N * K; e += nthr) {
                 const int n = e / K, kp = e - n * K;
                 const int k = (kp == K - 1) ? 0 : kp + 1;
-                Imk[(long)n * ldk + kp] = imk(n, k, g, ex, mk, Nk);
+                Imk[(long)n * ldk + kp] = imk(HARM(n), k, g, ex, mk, Nk);
             }
         }
         for (int kp = tid; kp < K; kp += nthr) {
@@ -873,15 +979,26 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         PHASE_END(PH_IMK);
         // 2./3. [T ; -r_i ; q_j] = [H | u'_i | w_j]^T-contraction with Imk: rows N.. of the product are the right-hand
         // sides r_i = -(bc_i Imk[0][:] + Imk^T u_i) (augmented rows of P) and q_j = Imk^T w_j
-        cta_gemm_dmma(HT, ldn, Imk, ldk, N + 2 * R, K, N, false, sm, [&](int m, int n, double v0, double v1) {
-            if (n >= K) return;
-            if (m < N) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
-            else if (m < N + R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(-v0, -v1);
-            else if (m < N + 2 * R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(v0, v1);
-        });
+        // Factorised form: [-r_i ; q_j ; W] = LA^T-contraction with the row-permuted Imk, W = L^T Imk; output rows
+        // 2R + m only need contraction rows k >= m (L is lower trapezoidal), which the GEMM skips chunk-wise.
+        if (lmode) {
+            cta_gemm_dmma(LA, ldn, Imk, ldk, 2 * R + hrank, K, N, false, 2 * R, sm, [&](int m, int n, double v0, double v1) {
+                if (n >= K) return;
+                if (m < R) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = make_double2(-v0, -v1);
+                else if (m < 2 * R) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = make_double2(v0, v1);
+                else if (m < 2 * R + hrank) *reinterpret_cast<double2*>(T + (long)(m - 2 * R) * ldk + n) = make_double2(v0, v1);
+            });
+        } else {
+            cta_gemm_dmma(HT, ldn, Imk, ldk, N + 2 * R, K, N, false, -1, sm, [&](int m, int n, double v0, double v1) {
+                if (n >= K) return;
+                if (m < N) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
+                else if (m < N + R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(-v0, -v1);
+                else if (m < N + 2 * R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(v0, v1);
+            });
+        }
         PHASE_END(PH_GEMM1);
-        // 4. P = Imk^T T - Re(D), lower triangle
-        cta_gemm_dmma(Imk, ldk, T, ldk, K, K, N, true, sm, [&](int m, int n, double v0, double v1) {
+        // 4. P = Imk^T T - Re(D)  (= W^T W - Re(D) in the factorised form), lower triangle
+        cta_gemm_dmma(lmode ? T : Imk, ldk, T, ldk, K, K, lmode ? hrank : N, true, -1, sm, [&](int m, int n, double v0, double v1) {
             if (m < K && n <= m) {
                 if (m == n) v0 -= ext[m];
                 if (m == n + 1) v1 -= ext[m];
@@ -915,6 +1032,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
 
 // RESIDENT: the packed P (+ right-hand-side rows) is pulled into shared memory with one bulk copy and the whole
 // factorisation / back-substitution runs there (K <= ~208 at one CTA per SM); otherwise P stays in its L2-resident buffer.
+#undef HARM
 template <int THREADS, int MINB, bool RESIDENT>
 __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -1413,7 +1531,7 @@ struct meemb200_plan {
     std::vector<GeomDesc> geoms;
     int n_slots_geom, n_slots_work;
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
-    size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop;
+    size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
     int algo;
     bool use_coop;          // grid-cooperative geometry stage (few large geometries)
     int64_t wave_items;     // systems per frequency-stage wave
@@ -1567,6 +1685,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     // Resident by default only while >= 5 CTAs still fit an SM (K <~ 75): the factorisation is a latency chain (13 panels
     // at K = 200, each with a 16-step register Cholesky) that is hidden by CTAs in flight, not by threads per CTA -
     // measured on big_tricylinder: L2-resident 5 CTAs/SM 2.9 ms, shared-memory-resident 1 CTA/SM x 512 threads 3.0 ms.
+    P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
+    if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     const bool fits = P->smem_chol + 2048 <= limit;
     P->solve_variant = (fits && P->smem_chol <= 44 * 1024) ? 1 : 0;
     if (const char* ev = getenv("MEEMB200_SOLVE_VARIANT")) {      // tuning / test override
@@ -1659,7 +1779,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
-    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 5 + 2 * P->n_waves : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
+    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 6 + 2 * P->n_waves : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
     *out = P;
@@ -1787,6 +1907,11 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
     CUDA_TRY(cudaGetLastError());
     if (h->algo != MEEMB200_ALGO_DENSE) {
         CUDA_TRY(P->nb_geom == 8 ? launch_geom<8>(P, d_in, d_ws, s) : P->nb_geom == 4 ? launch_geom<4>(P, d_in, d_ws, s) : launch_geom<2>(P, d_in, d_ws, s));
+        if (h->algo == MEEMB200_ALGO_SCHUR) {
+            CUDA_TRY(cudaFuncSetAttribute(k_hchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(P->smem_hchol, 1024)));
+            k_hchol<<<std::min(h->n_geom, 8 * P->ctx->sm_count), kHcholThreads, std::max<size_t>(P->smem_hchol, 1024), s>>>(d_in, d_ws, (unsigned)P->smem_hchol);
+            CUDA_TRY(cudaGetLastError());
+        }
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
         CUDA_TRY(P->nb_freq == 8 ? launch_freq<8>(P, d_in, d_ws, o, s) : P->nb_freq == 4 ? launch_freq<4>(P, d_in, d_ws, o, s) : launch_freq<2>(P, d_in, d_ws, o, s));
     } else {
