@@ -290,6 +290,8 @@ def main():
         phase_share = {k: (round(v, 4) if isinstance(v, float) else v) for k, v in plan.phase_profile().items()} if args.algo == "schur" else None
         F_ = len(omegas)
 
+        factorised = args.algo == "schur" and plan.factorised_geometries() == len(flat)
+
         def kernel_flops(g):   # closed-form real FP64 flops per kernel for geometry g (kernel table)
             N, K, R, p = float(g.NMK[-2]), float(g.NMK[-1]), float(g.R), float(g.size - g.NMK[-1])
             NT = float(g.size)
@@ -297,8 +299,11 @@ def main():
                 return {"frequency": F_ * (8 / 3 * NT ** 3 + 8 * NT * NT * R)}
             geom = 2 / 3 * p ** 3 + 2 * p * p * (N + R)
             if args.algo == "schur":
-                return {"geometry": geom, "freq_gemm": F_ * (2 * N * N * K + N * K * K),
-                        "freq_solve": F_ * (K ** 3 / 3 + 2 * K * K * (R + 1) + 4 * K * R)}
+                # factorised-H form (k_hchol): W = L^T Imk triangular (N^2 K) + right-hand-side rows (4 R N K) + W^T W lower (N K^2);
+                # H itself when it did not factorise: 2 N^2 K + N K^2
+                gemm = (N * N * K + 4 * R * N * K + N * K * K) if factorised else (2 * N * N * K + N * K * K)
+                return {"geometry": geom + (N ** 3 / 3 if factorised else 0.0), "freq_gemm": F_ * gemm,
+                        "freq_solve": F_ * (K ** 3 / 3 + 2 * K * K * R + 2 * K * R * R)}     # Cholesky + 2R forward solves + dots
             return {"geometry": geom, "frequency": F_ * (2 * N * N * K + 2 * N * K * K + 2 / 3 * K ** 3 + 2 * K * K * (1 + 2 * R) + 4 * N * K * R)}
         kf = {}
         for g in flat:

@@ -164,7 +164,8 @@ int meemb200_fp64_peak(meemb200_ctx* ctx, int32_t kind, double* flops, void* str
 int meemb200_last_timing(meemb200_plan* plan, float ms[5]);
 
 /* Per-phase SM-cycle totals (summed over CTAs) of the frequency-stage kernel of the most recent
- * meemb200_solve that used `d_workspace`: [0] coupling table, [1] column dots / right-hand sides,
+ * meemb200_solve that used `d_workspace`: [0] coupling table, [1] NOT cycles: number of geometries whose H was
+ * Cholesky-factorised (k_hchol) and whose frequency GEMM therefore ran the W = L^T Imk form,
  * [2] T = H Imk, [3] Imk^T T, [4] Cholesky, [5] back-substitution, [6] coefficients, [7] X;
  * [8..13] cooperative geometry stage as seen by CTA 0: [8] panel factorisation (owner CTAs), [9] factor + grid
  * barrier, [10] trailing update, [11] barrier after update, [12] back-substitution, [13] back-substitution + barrier.

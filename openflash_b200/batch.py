@@ -220,10 +220,19 @@ class BatchPlan:
         cyc = (C.c_double * 16)()
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.lib.meemb200_phase_profile(self.plan, self.d_ws.data_ptr(), cyc, C.c_void_p(stream)))
+        cyc[1] = 0.0                      # slot 1 counts factorised geometries (k_hchol), not cycles
         tot = sum(cyc[:8]) or 1.0
         out = {k: cyc[i] / tot for i, k in enumerate(self.PHASES)}
         out["coop_geom_cycles"] = [cyc[i] for i in range(8, 16)]
         return out
+
+    def factorised_geometries(self):
+        """Number of geometries of the last solve whose coupling matrix H was Cholesky-factorised (k_hchol), i.e. that ran
+        the W = L^T Imk form of the frequency GEMM (measurement only)."""
+        cyc = (C.c_double * 16)()
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.meemb200_phase_profile(self.plan, self.d_ws.data_ptr(), cyc, C.c_void_p(stream)))
+        return int(cyc[1])
 
     def download(self):
         """Device->host read of all outputs; returns flat numpy arrays."""

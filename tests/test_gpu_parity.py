@@ -236,3 +236,30 @@ def test_geometry_sweep_c4_vs_oracle(ofb):
     for g, r in zip(gs, res):
         og = mo.FlatGeometry(g["h"], g["a"], g["d"], g["NMK"])
         _check(r, mo.run_sweep(og, om, g["body_map"], g["modes"]))
+
+
+@pytest.mark.parametrize("env", [{"MEEMB200_SOLVE_VARIANT": "0"}, {"MEEMB200_SOLVE_VARIANT": "1"}, {"MEEMB200_SOLVE_VARIANT": "2"},
+                                 {"MEEMB200_SOLVE_VARIANT": "3"}, {"MEEMB200_NO_HCHOL": "1"}],
+                         ids=lambda e: "-".join(f"{k[9:]}={v}" for k, v in e.items()))
+@pytest.mark.parametrize("name", sorted(META2))
+def test_schur_kernel_variants_vs_reference(ofb, monkeypatch, name, env):
+    """Every k_freq_solve variant (P in its L2 buffer / resident in shared memory at 128, 256, 512 threads) and the
+    unfactorised-H form of k_freq_gemm meet the same bar as the default path, X included (the overrides are read at plan
+    creation)."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    s = META2[name]
+    geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
+    res = ofb.solve_batch([geo], s["omegas"], algo=ofb.ALGO_SCHUR, want_x=True)[0]
+    assert np.all(res["status"] == 0)
+    ref = {v: Z2[f"{name}/{v}"] for v in ("added_mass", "damping", "excitation_force", "excitation_phase")}
+    _check(res, ref)
+    pot = Z2[f"{name}/potentials"]
+    NMK, col = s["NMK"], 0
+    for dom in range(len(NMK)):
+        width = NMK[dom] if dom in (0, len(NMK) - 1) else 2 * NMK[dom]
+        refp = pot[:, :, dom, :width]
+        assert np.max(np.abs(res["X"][:, :, col:col + width] - refp)) <= 1e-9 * np.max(np.abs(refp))
+        col += width
+    res2 = ofb.solve_batch([geo], s["omegas"], algo=ofb.ALGO_SCHUR)[0]          # coefficient-only path (no back-substitution)
+    _check(res2, ref)
