@@ -44,27 +44,45 @@ constexpr int kGemmLdA = kGemmTM + 4, kGemmLdB = kGemmTN + 4;
 constexpr int kGemmStageDoubles = kGemmKC * (kGemmLdA + kGemmLdB);
 constexpr size_t kGemmSmemBytes = 2 * kGemmStageDoubles * sizeof(double);
 
-__device__ __forceinline__ void gemm_stage_load(double* st, const double* A, int lda, const double* B, int ldb,
-                                                int m0, int n0, int Mlim, int Nlim, int k0, int Kd) {
+// Thread t copies 16-byte group (t & 31) of A rows (t >> 5) + 8 it and group (t & 63) of B rows (t >> 6) + 4 it, so the
+// per-thread source pointers / column predicates are chunk-invariant (GemmStageMap, built once per CTA tile) and a chunk
+// only adds k0 rows: ~4 instructions per cp.async instead of ~30 of index arithmetic.
+struct GemmStageMap {
+    const double* pa;     // A + (t >> 5) * lda + m0 + 2 (t & 31)
+    const double* pb;     // B + (t >> 6) * ldb + n0 + 2 (t & 63)
+    unsigned sa, sb;      // shared-memory byte offsets of the two destinations inside a stage
+    bool oka, okb;        // column inside the matrix
+};
+__device__ __forceinline__ GemmStageMap gemm_stage_map(const double* A, int lda, const double* B, int ldb,
+                                                       int m0, int n0, int Mlim, int Nlim) {
     const int tid = threadIdx.x;
-    double* As = st;
-    double* Bs = st + kGemmKC * kGemmLdA;
-    // A chunk: KC rows x 64 doubles = 32 x 16-byte groups per row
+    GemmStageMap mp;
+    const int ra = tid >> 5, ga = tid & 31, rb = tid >> 6, gb = tid & 63;
+    mp.oka = (m0 + 2 * ga) < Mlim;
+    mp.okb = (n0 + 2 * gb) < Nlim;
+    mp.pa = mp.oka ? A + (long)ra * lda + m0 + 2 * ga : A;
+    mp.pb = mp.okb ? B + (long)rb * ldb + n0 + 2 * gb : B;
+    mp.sa = (unsigned)((ra * kGemmLdA + 2 * ga) * sizeof(double));
+    mp.sb = (unsigned)((kGemmKC * kGemmLdA + rb * kGemmLdB + 2 * gb) * sizeof(double));
+    return mp;
+}
+__device__ __forceinline__ void cp_async16s(unsigned smem_dst, const void* gsrc, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(src_bytes));
+}
+__device__ __forceinline__ void gemm_stage_load(double* st, const GemmStageMap& mp, int lda, int ldb, int k0, int Kd) {
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(st);
+    const int ra = threadIdx.x >> 5, rb = threadIdx.x >> 6;
+    const double* pa = mp.pa + (long)k0 * lda;
+    const double* pb = mp.pb + (long)k0 * ldb;
 #pragma unroll
-    for (int it = 0; it < (kGemmKC * kGemmTM / 2) / 256; ++it) {
-        const int idx = tid + it * 256;
-        const int r = idx >> 5, g = idx & 31;
-        const int k = k0 + r, m = m0 + 2 * g;
-        const bool ok = (k < Kd) && (m < Mlim);
-        cp_async16(As + r * kGemmLdA + 2 * g, ok ? (A + (long)k * lda + m) : A, ok ? 16 : 0);
+    for (int it = 0; it < kGemmKC / 8; ++it) {
+        const bool ok = mp.oka && (k0 + ra + 8 * it < Kd);
+        cp_async16s(s0 + mp.sa + it * 8 * kGemmLdA * (unsigned)sizeof(double), ok ? pa + (long)it * 8 * lda : pa, ok ? 16 : 0);
     }
 #pragma unroll
-    for (int it = 0; it < (kGemmKC * kGemmTN / 2) / 256; ++it) {
-        const int idx = tid + it * 256;
-        const int r = idx >> 6, g = idx & 63;
-        const int k = k0 + r, n = n0 + 2 * g;
-        const bool ok = (k < Kd) && (n < Nlim);
-        cp_async16(Bs + r * kGemmLdB + 2 * g, ok ? (B + (long)k * ldb + n) : B, ok ? 16 : 0);
+    for (int it = 0; it < kGemmKC / 4; ++it) {
+        const bool ok = mp.okb && (k0 + rb + 4 * it < Kd);
+        cp_async16s(s0 + mp.sb + it * 4 * kGemmLdB * (unsigned)sizeof(double), ok ? pb + (long)it * 4 * ldb : pb, ok ? 16 : 0);
     }
 }
 
@@ -124,13 +142,13 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
                 for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
             __syncthreads();      // previous users of the stage buffers are done
             const int c0 = (tri >= 0 && m0 > tri) ? (m0 - tri) / kGemmKC : 0;
-            gemm_stage_load(sm + (c0 & 1) * kGemmStageDoubles, A, lda, B, ldb, m0, n0, Mlim, Nlim, c0 * kGemmKC, Kd);
+            const GemmStageMap mp = gemm_stage_map(A, lda, B, ldb, m0, n0, Mlim, Nlim);
+            gemm_stage_load(sm + (c0 & 1) * kGemmStageDoubles, mp, lda, ldb, c0 * kGemmKC, Kd);
             cp_async_commit();
             for (int c = c0; c < nchunk; ++c) {
                 double* cur = sm + (c & 1) * kGemmStageDoubles;
                 if (c + 1 < nchunk) {
-                    gemm_stage_load(sm + ((c + 1) & 1) * kGemmStageDoubles, A, lda, B, ldb, m0, n0, Mlim, Nlim,
-                                    (c + 1) * kGemmKC, Kd);
+                    gemm_stage_load(sm + ((c + 1) & 1) * kGemmStageDoubles, mp, lda, ldb, (c + 1) * kGemmKC, Kd);
                     cp_async_commit();
                     cp_async_wait<1>();
                 } else {
@@ -158,6 +176,154 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
                         if (i < nri && j < nci)
                             epi(m0 + (rb0 + i) * 8 + lr, n0 + (cb0 + j) * 8 + 2 * lc, acc[i][j][0], acc[i][j][1]);
             }
+        }
+    }
+    __syncthreads();
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Lower triangle of C = W^T W  (W: Kd x Nc row-major, leading dimension ldw), the symmetric rank-Kd update of the
+// factorised-H form of the frequency stage.  Unlike cta_gemm_dmma, whole-width chunks of W (kSyrkKC x Nc) are staged,
+// so a warp can own ANY 8x8-block rectangle of C: the lower triangle is cut into warp tiles of <= 4 x 4 blocks
+// (block groups a >= b; diagonal tiles a == b only compute their lower blocks and load one fragment set), the tiles
+// are sorted by size and dealt to the 8 warps pass by pass - 325 useful block products in 49 block-times per warp for
+// Nc = 200, against 64 for the rectangular 64 x 128 CTA tiles with warp-level skipping.
+constexpr int kSyrkKC = 16;
+constexpr int kSyrkMaxTiles = 96;
+struct SyrkPlan {                       // lives in static shared memory of the calling kernel
+    int nb, nt;
+    unsigned char ta[kSyrkMaxTiles], tb[kSyrkMaxTiles];
+};
+__host__ __device__ inline int syrk_lds(int Nc) { const int n8 = (Nc + 7) & ~7; return n8 + ((n8 & 15) ? 12 : 4); }   // = 4 (mod 16)
+__host__ __device__ inline bool syrk_fits(int Nc) {
+    const int nb = (Nc + 7) >> 3, ng = (nb + 3) >> 2;
+    return 2 * kSyrkKC * syrk_lds(Nc) <= 2 * kGemmStageDoubles && ng * (ng + 1) / 2 <= kSyrkMaxTiles;
+}
+
+template <int NI, int NJ>
+__device__ __forceinline__ void syrk_chunk(const double* As, const double* Bs, int ld, int lc, double (&acc)[4][4][2]) {
+#pragma unroll
+    for (int ks = 0; ks < kSyrkKC / 4; ++ks) {
+        double af[NI], bf[NJ];
+#pragma unroll
+        for (int i = 0; i < NI; ++i) af[i] = As[(ks * 4 + lc) * ld + i * 8];
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) bf[j] = Bs[(ks * 4 + lc) * ld + j * 8];
+#pragma unroll
+        for (int i = 0; i < NI; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+}
+// diagonal tile: rows == columns, only blocks j <= i
+template <int NI>
+__device__ __forceinline__ void syrk_chunk_diag(const double* As, int ld, int lc, double (&acc)[4][4][2]) {
+#pragma unroll
+    for (int ks = 0; ks < kSyrkKC / 4; ++ks) {
+        double af[NI];
+#pragma unroll
+        for (int i = 0; i < NI; ++i) af[i] = As[(ks * 4 + lc) * ld + i * 8];
+#pragma unroll
+        for (int i = 0; i < NI; ++i)
+#pragma unroll
+            for (int j = 0; j <= i; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], af[j]);
+    }
+}
+
+// warp w copies rows w, w + nwarp, ...; lanes stride over the 16-byte groups of a row (no index division)
+__device__ __forceinline__ void syrk_stage_load(double* st, int lds, const double* W, int ldw, int n8, int k0, int Kd) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const int gpr = n8 >> 1;                      // 16-byte groups per row
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(st);
+    for (int r = warp; r < kSyrkKC; r += nwarp) {
+        const bool ok = (k0 + r) < Kd;
+        const double* src = ok ? W + (long)(k0 + r) * ldw : W;
+        const unsigned dst = s0 + (unsigned)(r * lds) * (unsigned)sizeof(double);
+        for (int g = lane; g < gpr; g += 32) cp_async16s(dst + 16u * g, ok ? src + 2 * g : src, ok ? 16 : 0);
+    }
+}
+
+template <class Epi>
+__device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int Kd, double* sm, SyrkPlan& plan, Epi epi) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int nb = (Nc + 7) >> 3, n8 = nb * 8, lds = syrk_lds(Nc);
+    const int ng = (nb + 3) >> 2;
+    const int nchunk = (Kd + kSyrkKC - 1) / kSyrkKC;
+    __syncthreads();
+    if (plan.nb != nb) {                         // (re)build the sorted tile list: once per CTA for a uniform batch
+        if (threadIdx.x == 0) {
+            int nt = 0;
+            for (int a = 0; a < ng; ++a)
+                for (int b = 0; b <= a; ++b) {
+                    const int ga = (a + 1) * nb / ng - a * nb / ng, gb = (b + 1) * nb / ng - b * nb / ng;
+                    const int sz = (a == b) ? ga * (ga + 1) / 2 : ga * gb;
+                    int pos = nt++;
+                    while (pos > 0) {            // insertion sort, largest first
+                        const int pa = plan.ta[pos - 1], pb = plan.tb[pos - 1];
+                        const int qa = (pa + 1) * nb / ng - pa * nb / ng, qb = (pb + 1) * nb / ng - pb * nb / ng;
+                        const int psz = (pa == pb) ? qa * (qa + 1) / 2 : qa * qb;
+                        if (psz >= sz) break;
+                        plan.ta[pos] = pa; plan.tb[pos] = pb; --pos;
+                    }
+                    plan.ta[pos] = (unsigned char)a; plan.tb[pos] = (unsigned char)b;
+                }
+            plan.nt = nt;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) plan.nb = nb;
+    }
+    const int nt = plan.nt;
+    for (int t0 = 0; t0 < nt; t0 += nwarp) {
+        const int t = t0 + warp;
+        const bool has = t < nt;
+        const int a = has ? plan.ta[t] : 0, b = has ? plan.tb[t] : 0;
+        const int rb0 = a * nb / ng, rb1 = (a + 1) * nb / ng, cb0 = b * nb / ng, cb1 = (b + 1) * nb / ng;
+        const int nri = rb1 - rb0, nci = cb1 - cb0;
+        const int shape = !has ? -1 : (a == b ? 16 + (nri - 1) : (nri - 1) * 4 + (nci - 1));
+        double acc[4][4][2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        __syncthreads();      // previous users of the stage buffers are done
+        syrk_stage_load(sm, lds, W, ldw, n8, 0, Kd);
+        cp_async_commit();
+        for (int c = 0; c < nchunk; ++c) {
+            double* cur = sm + (c & 1) * kSyrkKC * lds;
+            if (c + 1 < nchunk) {
+                syrk_stage_load(sm + ((c + 1) & 1) * kSyrkKC * lds, lds, W, ldw, n8, (c + 1) * kSyrkKC, Kd);
+                cp_async_commit();
+                cp_async_wait<1>();
+            } else {
+                cp_async_wait<0>();
+            }
+            __syncthreads();
+            const double* As = cur + rb0 * 8 + lr;
+            const double* Bs = cur + cb0 * 8 + lr;
+            switch (shape) {
+#define MEEM_SYRK_CASE(NI, NJ) case (NI - 1) * 4 + (NJ - 1): syrk_chunk<NI, NJ>(As, Bs, lds, lc, acc); break;
+                MEEM_SYRK_CASE(1, 1) MEEM_SYRK_CASE(1, 2) MEEM_SYRK_CASE(1, 3) MEEM_SYRK_CASE(1, 4)
+                MEEM_SYRK_CASE(2, 1) MEEM_SYRK_CASE(2, 2) MEEM_SYRK_CASE(2, 3) MEEM_SYRK_CASE(2, 4)
+                MEEM_SYRK_CASE(3, 1) MEEM_SYRK_CASE(3, 2) MEEM_SYRK_CASE(3, 3) MEEM_SYRK_CASE(3, 4)
+                MEEM_SYRK_CASE(4, 1) MEEM_SYRK_CASE(4, 2) MEEM_SYRK_CASE(4, 3) MEEM_SYRK_CASE(4, 4)
+#undef MEEM_SYRK_CASE
+                case 16: syrk_chunk_diag<1>(As, lds, lc, acc); break;
+                case 17: syrk_chunk_diag<2>(As, lds, lc, acc); break;
+                case 18: syrk_chunk_diag<3>(As, lds, lc, acc); break;
+                case 19: syrk_chunk_diag<4>(As, lds, lc, acc); break;
+                default: break;
+            }
+            __syncthreads();
+        }
+        if (has) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (i < nri && j < nci && (a != b || j <= i))
+                        epi((rb0 + i) * 8 + lr, (cb0 + j) * 8 + 2 * lc, acc[i][j][0], acc[i][j][1]);
         }
     }
     __syncthreads();

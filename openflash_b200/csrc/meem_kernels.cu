@@ -846,11 +846,14 @@ enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, 
 #define PHASE_END_S(ph) PHASE_END(ph)
 #endif
 
-__global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws, int item0, int item1, int* counter) {
+__global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws, int item0, int item1, int* counter, int flags) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
     __shared__ int sh_item, sh_row0;
+    __shared__ SyrkPlan sh_syrk;
+    if (threadIdx.x == 0) sh_syrk.nb = -1;
+    const bool use_syrk = (flags & 1) == 0;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -998,13 +1001,15 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         }
         PHASE_END(PH_GEMM1);
         // 4. P = Imk^T T - Re(D)  (= W^T W - Re(D) in the factorised form), lower triangle
-        cta_gemm_dmma(lmode ? T : Imk, ldk, T, ldk, K, K, lmode ? hrank : N, true, -1, sm, [&](int m, int n, double v0, double v1) {
+        auto store_p = [&](int m, int n, double v0, double v1) {
             if (m < K && n <= m) {
                 if (m == n) v0 -= ext[m];
                 if (m == n + 1) v1 -= ext[m];
                 *reinterpret_cast<double2*>(P + tri_off(m) + n) = make_double2(v0, v1);
             }
-        });
+        };
+        if (lmode && use_syrk && K >= 64 && syrk_fits(K)) cta_syrk_dmma(T, ldk, K, hrank, sm, sh_syrk, store_p);
+        else cta_gemm_dmma(lmode ? T : Imk, ldk, T, ldk, K, K, lmode ? hrank : N, true, -1, sm, store_p);
         PHASE_END(PH_GEMM2);
     }
     if (tid == 0) {
@@ -1529,7 +1534,8 @@ struct meemb200_plan {
     const BlobHeader* hdr() const { return reinterpret_cast<const BlobHeader*>(blob.data()); }
     MeemPlanInfo info;
     std::vector<GeomDesc> geoms;
-    int n_slots_geom, n_slots_work;
+    int n_slots_geom, n_slots_work, geom_threads;
+    int gemm_flags;         // k_freq_gemm: bit 0 = rectangular-tile P = W^T W instead of the warp-tile-queue SYRK (tuning / tests)
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
     int algo;
@@ -1687,6 +1693,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     // measured on big_tricylinder: L2-resident 5 CTAs/SM 2.9 ms, shared-memory-resident 1 CTA/SM x 512 threads 3.0 ms.
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
+    P->gemm_flags = getenv("MEEMB200_NO_SYRK") ? 1 : 0;
     const bool fits = P->smem_chol + 2048 <= limit;
     P->solve_variant = (fits && P->smem_chol <= 44 * 1024) ? 1 : 0;
     if (const char* ev = getenv("MEEMB200_SOLVE_VARIANT")) {      // tuning / test override
@@ -1715,7 +1722,11 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->smem_dense = P->nb_dense ? nb_bytes<cplx>(P->nb_dense, max_NT) : 0;
     const int sms = ctx->sm_count;
     const int64_t n_sys = (int64_t)G * F;
-    P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, sms);
+    // One CTA per geometry is a latency chain (pivot search, row swaps and panel staging through L2): small geometries run
+    // 256-thread CTAs, several per SM (register-limited), large ones 512 threads
+    P->geom_threads = max_p <= 320 ? 256 : 512;
+    if (const char* ev = getenv("MEEMB200_GEOM_THREADS")) { const int t = atoi(ev); if (t == 128 || t == 256 || t == 512) P->geom_threads = t; }
+    P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, (int64_t)sms * (512 / P->geom_threads));
     if (schur) {
         const int per_sm = (std::max(P->smem_freq + 24 * 1024, kGemmSmemBytes + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
@@ -1826,7 +1837,7 @@ template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* i
     if (P->use_coop) return launch_geom_coop(P, in, ws, s);
     cudaError_t e = cudaFuncSetAttribute(k_geom<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
     if (e != cudaSuccess) return e;
-    k_geom<NB><<<P->n_slots_geom, 512, P->smem_geom, s>>>(in, ws, 0);
+    k_geom<NB><<<P->n_slots_geom, P->geom_threads, P->smem_geom, s>>>(in, ws, 0);
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
@@ -1856,7 +1867,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
         for (int w = 0; w < P->n_waves; ++w) {
             const int item0 = (int)(w * P->wave_items), item1 = (int)std::min<int64_t>(n_sys, (w + 1) * P->wave_items);
             const int n = item1 - item0;
-            k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w);
+            k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w, P->gemm_flags);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[3], s);
             ksolve<<<std::min(n, P->solve_grid), nthr_solve, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[4], s);
