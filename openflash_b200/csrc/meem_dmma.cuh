@@ -32,17 +32,20 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // C[m][n] = sum_k A[k][m] * B[k][n]   ("TN": both operands stored contraction-major, row-major with
 // leading dimensions lda / ldb, which must be even and the base pointers 16-byte aligned).
 // 256 threads = 8 warps as a 2 x 4 grid of 32 x 32 warp tiles -> CTA tile 64 x 128; contraction is
-// consumed in chunks of kGemmKC rows through a 2-stage cp.async pipeline.  Columns of A / B beyond
+// consumed in chunks of kGemmKC rows through a kGemmStages-deep cp.async ring.  Columns of A / B beyond
 // Mm / Nn (up to the even-padded leading dimension) may hold anything finite or not: they only feed
 // output rows / columns that are never stored.  Rows beyond Kd are zero-filled.
 // lower_only: skip 8x8 blocks that lie strictly above the diagonal (m < n for every element).
 // epi(m, n, v0, v1): called once per lane per stored 8x8 block with the two adjacent columns
 // n, n+1 of row m (n is even); bounds (m < Mm, n < Nn, n+1 < Nn) are the callee's to check.
-constexpr int kGemmKC = 32;
+constexpr int kGemmKC = 16;
+constexpr int kGemmStages = 3;          // cp.async ring: one barrier per chunk (the stage refilled at chunk c is the one read at c - 1)
 constexpr int kGemmTM = 64, kGemmTN = 128;
 constexpr int kGemmLdA = kGemmTM + 4, kGemmLdB = kGemmTN + 4;
 constexpr int kGemmStageDoubles = kGemmKC * (kGemmLdA + kGemmLdB);
-constexpr size_t kGemmSmemBytes = 2 * kGemmStageDoubles * sizeof(double);
+constexpr int kGemmSmemDoubles = 12800;                                  // dynamic shared memory of k_freq_gemm (2 CTAs / SM)
+constexpr size_t kGemmSmemBytes = kGemmSmemDoubles * sizeof(double);
+static_assert(kGemmStages * kGemmStageDoubles <= kGemmSmemDoubles, "cp.async ring does not fit");
 
 // Thread t copies 16-byte group (t & 31) of A rows (t >> 5) + 8 it and group (t & 63) of B rows (t >> 6) + 4 it, so the
 // per-thread source pointers / column predicates are chunk-invariant (GemmStageMap, built once per CTA tile) and a chunk
@@ -75,12 +78,12 @@ __device__ __forceinline__ void gemm_stage_load(double* st, const GemmStageMap& 
     const double* pa = mp.pa + (long)k0 * lda;
     const double* pb = mp.pb + (long)k0 * ldb;
 #pragma unroll
-    for (int it = 0; it < kGemmKC / 8; ++it) {
+    for (int it = 0; it < kGemmKC / 8; ++it) {        // rows (t >> 5) + 8 it
         const bool ok = mp.oka && (k0 + ra + 8 * it < Kd);
         cp_async16s(s0 + mp.sa + it * 8 * kGemmLdA * (unsigned)sizeof(double), ok ? pa + (long)it * 8 * lda : pa, ok ? 16 : 0);
     }
 #pragma unroll
-    for (int it = 0; it < kGemmKC / 4; ++it) {
+    for (int it = 0; it < kGemmKC / 4; ++it) {        // rows (t >> 6) + 4 it
         const bool ok = mp.okb && (k0 + rb + 4 * it < Kd);
         cp_async16s(s0 + mp.sb + it * 4 * kGemmLdB * (unsigned)sizeof(double), ok ? pb + (long)it * 4 * ldb : pb, ok ? 16 : 0);
     }
@@ -143,18 +146,17 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
             __syncthreads();      // previous users of the stage buffers are done
             const int c0 = (tri >= 0 && m0 > tri) ? (m0 - tri) / kGemmKC : 0;
             const GemmStageMap mp = gemm_stage_map(A, lda, B, ldb, m0, n0, Mlim, Nlim);
-            gemm_stage_load(sm + (c0 & 1) * kGemmStageDoubles, mp, lda, ldb, c0 * kGemmKC, Kd);
+            // prologue: chunks c0, c0 + 1 in flight (a group is committed every step so that wait_group counts stay uniform)
+            gemm_stage_load(sm + (c0 % kGemmStages) * kGemmStageDoubles, mp, lda, ldb, c0 * kGemmKC, Kd);
+            cp_async_commit();
+            if (c0 + 1 < nchunk) gemm_stage_load(sm + ((c0 + 1) % kGemmStages) * kGemmStageDoubles, mp, lda, ldb, (c0 + 1) * kGemmKC, Kd);
             cp_async_commit();
             for (int c = c0; c < nchunk; ++c) {
-                double* cur = sm + (c & 1) * kGemmStageDoubles;
-                if (c + 1 < nchunk) {
-                    gemm_stage_load(sm + ((c + 1) & 1) * kGemmStageDoubles, mp, lda, ldb, (c + 1) * kGemmKC, Kd);
-                    cp_async_commit();
-                    cp_async_wait<1>();
-                } else {
-                    cp_async_wait<0>();
-                }
-                __syncthreads();
+                cp_async_wait<1>();                  // chunk c has landed (this thread's copies)
+                __syncthreads();                     // ... everyone's; and every warp is done with chunk c - 1
+                if (c + 2 < nchunk) gemm_stage_load(sm + ((c + 2) % kGemmStages) * kGemmStageDoubles, mp, lda, ldb, (c + 2) * kGemmKC, Kd);
+                cp_async_commit();
+                const double* cur = sm + (c % kGemmStages) * kGemmStageDoubles;
                 const double* As = cur + rb0 * 8 + lr;
                 const double* Bs = cur + kGemmKC * kGemmLdA + cb0 * 8 + lr;
                 switch (shape) {
@@ -166,8 +168,8 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
 #undef MEEM_GEMM_CASE
                     default: break;
                 }
-                __syncthreads();
             }
+            cp_async_wait<0>();
             if (shape >= 0) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
@@ -198,7 +200,7 @@ struct SyrkPlan {                       // lives in static shared memory of the 
 __host__ __device__ inline int syrk_lds(int Nc) { const int n8 = (Nc + 7) & ~7; return n8 + ((n8 & 15) ? 12 : 4); }   // = 4 (mod 16)
 __host__ __device__ inline bool syrk_fits(int Nc) {
     const int nb = (Nc + 7) >> 3, ng = (nb + 3) >> 2;
-    return 2 * kSyrkKC * syrk_lds(Nc) <= 2 * kGemmStageDoubles && ng * (ng + 1) / 2 <= kSyrkMaxTiles;
+    return kGemmStages * kSyrkKC * syrk_lds(Nc) <= kGemmSmemDoubles && ng * (ng + 1) / 2 <= kSyrkMaxTiles;
 }
 
 template <int NI, int NJ>
@@ -290,16 +292,14 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
         __syncthreads();      // previous users of the stage buffers are done
         syrk_stage_load(sm, lds, W, ldw, n8, 0, Kd);
         cp_async_commit();
+        if (1 < nchunk) syrk_stage_load(sm + kSyrkKC * lds, lds, W, ldw, n8, kSyrkKC, Kd);
+        cp_async_commit();
         for (int c = 0; c < nchunk; ++c) {
-            double* cur = sm + (c & 1) * kSyrkKC * lds;
-            if (c + 1 < nchunk) {
-                syrk_stage_load(sm + ((c + 1) & 1) * kSyrkKC * lds, lds, W, ldw, n8, (c + 1) * kSyrkKC, Kd);
-                cp_async_commit();
-                cp_async_wait<1>();
-            } else {
-                cp_async_wait<0>();
-            }
+            cp_async_wait<1>();
             __syncthreads();
+            if (c + 2 < nchunk) syrk_stage_load(sm + ((c + 2) % kGemmStages) * kSyrkKC * lds, lds, W, ldw, n8, (c + 2) * kSyrkKC, Kd);
+            cp_async_commit();
+            const double* cur = sm + (c % kGemmStages) * kSyrkKC * lds;
             const double* As = cur + rb0 * 8 + lr;
             const double* Bs = cur + cb0 * 8 + lr;
             switch (shape) {
@@ -315,8 +315,8 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
                 case 19: syrk_chunk_diag<4>(As, lds, lc, acc); break;
                 default: break;
             }
-            __syncthreads();
         }
+        cp_async_wait<0>();
         if (has) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)

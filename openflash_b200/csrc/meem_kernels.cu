@@ -898,7 +898,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         // sines, four divisions and a square root.  Both forms carry ~1e-13 absolute argument-rounding noise in the
         // sines (|theta| eps, theta up to ~1e3); the exact-equality branch |m_k| == lambda is kept.  Row m = 0 and
         // column k = 0 go through the reference-ordered imk().  (meemb200_assemble keeps imk() for every entry.)
-        const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= 2 * kGemmStageDoubles;
+        const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= kGemmSmemDoubles;
         if (fast) {
             double* tmk = sm;               // [K] m_k (permuted)
             double* tsk = tmk + K;          // sin(m_k L)
