@@ -1231,6 +1231,155 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
 #undef PHASE_END
 
 // ------------------------------------------------------------------------------------------------
+// Schur path, frequency stage for SMALL systems (N <= 16, K <= 16, R <= 4, no X output): one WARP per (geometry, omega)
+// system, everything in the warp's slice of shared memory - coupling table, [-r; q; W] = LA^T Imk, P = W^T W - Re D,
+// the register-resident 16 x 16 Cholesky (warp_chol16), forward solves as products with the inverse factor, Sherman-
+// Morrison closure and coefficients.  No CTA barriers, no HBM round trip between the stages: the design-sweep workload
+// (10^5 geometries x 64 omega at 16 modes per region) and the mini_bicylinder replica batch spend ~40 ns of SM time per
+// system here instead of a 256-thread CTA with 64 x 128 DMMA tiles per 16 x 16 system.
+constexpr int kSmallMax = 16, kSmallMaxR = 4, kSmallWarps = 4;
+struct SmallWs {
+    double Imk[kSmallMax][kSmallMax + 1];
+    double T[kSmallMax][kSmallMax + 1];
+    double Dg[kCholNB * (kCholNB + 1) + kCholNB];
+    double Li[kCholNB * kCholLdP];
+    double aug[2 * kSmallMaxR][kSmallMax];      // rows r_i then q_j; overwritten by their forward-solved forms
+    double ext[kSmallMax];
+    Exterior ex;
+    double beta;
+    int fail;
+};
+
+__global__ void __launch_bounds__(32 * kSmallWarps) k_freq_small(const void* blob, void* ws, OutPtrs out, int n_items, int* counter) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    DevView v = make_view(blob, ws);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    SmallWs& S = reinterpret_cast<SmallWs*>(smem)[warp];
+    const int F = v.hdr->n_freq;
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = atomicAdd(counter, 1);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= n_items) break;
+        const int gi = v.order[item / F], f = item % F;
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        const RootSet rs = v.sets[gd.root_set];
+        const double m0 = v.roots[rs.off + f];
+        const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+        const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+        const int N = gd.N, K = gd.K, R = gd.R, M = gd.M;
+        const int ldn = gs_ldn(N, R);
+        const double* gs = v.gstore + gd.gs_off;
+        const double* HT = gs;
+        const double* s0 = gs + (int64_t)N * ldn + 2LL * R * N;
+        const double* phi = s0 + R * R;
+        const double* bc = phi + R;
+        const int gstatus = (int)bc[R];
+        const int hrank = (int)bc[R + 1];
+        const bool lmode = hrank > 0;
+        const double* LA = gs + gs_base_doubles(N, R);
+        const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
+        __syncwarp();
+        if (lane == 0) { make_exterior(g, m0, S.ex); S.fail = 0; }
+        __syncwarp();
+        // 1. coupling table (reference-ordered imk for every entry), exterior diagonal; column order kp = k - 1, k = 0 last
+        for (int e = lane; e < N * K; e += 32) {
+            const int kk = e / K, kp = e - kk * K;
+            S.Imk[kk][kp] = imk(lmode ? perm[kk] : kk, (kp == K - 1) ? 0 : kp + 1, g, S.ex, mk, Nk);
+        }
+        if (lane < K) {
+            const cplx dg = ext_diag((lane == K - 1) ? 0 : lane + 1, g, S.ex, mk);
+            S.ext[lane] = dg.re;
+            if (lane == K - 1) S.beta = dg.im;
+        }
+        __syncwarp();
+        // 2. [-r_i ; q_j ; W] (factorised H) or [T ; -r_i ; q_j] (H itself): out[m][n] = sum_k A[k][m] Imk[k][n]
+        const double* A = lmode ? LA : HT;
+        const int nrow_t = lmode ? hrank : N;                 // rows of T / W
+        const int rows_out = nrow_t + 2 * R;
+        for (int e = lane; e < rows_out * K; e += 32) {
+            const int m = e / K, n = e - m * K;
+            double acc = 0.0;
+            for (int k = 0; k < N; ++k) acc = fma(A[(int64_t)k * ldn + m], S.Imk[k][n], acc);
+            int a = -1, trow = -1;                            // destination: aug row a (sign) or T row
+            if (lmode) { if (m < 2 * R) a = m; else trow = m - 2 * R; }
+            else { if (m < N) trow = m; else a = m - N; }
+            if (trow >= 0) S.T[trow][n] = acc;
+            else S.aug[a][n] = (a < R) ? -acc : acc;
+        }
+        __syncwarp();
+        // 3. P = A2^T T - Re(D), lower triangle, identity-padded to 16 x 16 in warp_chol16's layout
+        for (int e = lane; e < kCholNB * kCholNB; e += 32) {
+            const int m = e >> 4, n = e & 15;
+            double val = (m == n) ? 1.0 : 0.0;
+            if (m < K && n <= m) {
+                double acc = 0.0;
+                if (lmode) for (int k = 0; k < nrow_t; ++k) acc = fma(S.T[k][m], S.T[k][n], acc);
+                else for (int k = 0; k < N; ++k) acc = fma(S.Imk[k][m], S.T[k][n], acc);
+                val = (m == n) ? acc - S.ext[m] : acc;
+            } else if (m < K) val = 0.0;
+            S.Dg[m * (kCholNB + 1) + n] = val;
+        }
+        __syncwarp();
+        // 4. P = L L^T and L^{-1} in one warp
+        warp_chol16(S.Dg, S.Li, &S.fail);
+        __syncwarp();
+        // 5. forward solves fr_i = L^{-1} r_i, fq_j = L^{-1} q_j as products with the inverse factor
+        double fw[(2 * kSmallMaxR * kSmallMax + 31) / 32];
+#pragma unroll
+        for (int u = 0; u < (2 * kSmallMaxR * kSmallMax + 31) / 32; ++u) {
+            const int e = lane + 32 * u, a = e >> 4, c = e & 15;
+            double acc = 0.0;
+            if (a < 2 * R && c < K)
+                for (int q = 0; q <= c; ++q) acc = fma(S.Li[c * kCholLdP + q], S.aug[a][q], acc);
+            fw[u] = acc;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < (2 * kSmallMaxR * kSmallMax + 31) / 32; ++u) {
+            const int e = lane + 32 * u, a = e >> 4, c = e & 15;
+            if (a < 2 * R && c < K) S.aug[a][c] = fw[u];
+        }
+        __syncwarp();
+        // 6. coefficients (same closure as k_freq_solve)
+        const int status = gstatus | (S.fail ? 4 : 0);
+        const int64_t sysi = gd.out_sys + f;
+        if (lane == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
+        const double linv_last = S.Li[(K - 1) * kCholLdP + K - 1];
+        const double beta = S.beta;
+        const double ze = linv_last * linv_last;
+        const double den = 1.0 + beta * beta * ze * ze;
+        if (lane < R * R) {
+            const int j = lane / R, i = lane - j * R;
+            const double* fr = S.aug[i];
+            const double* fq = S.aug[R + j];
+            const double we = fr[K - 1] * linv_last;
+            const double xer = we / den, xei = we * beta * ze / den;
+            const double qz = fq[K - 1] * linv_last;
+            double qw = 0.0;
+            for (int k = 0; k < K; ++k) qw = fma(fq[k], fr[k], qw);
+            const double cre = 2.0 * kPi * ((s0[j * R + i] + (qw - beta * xei * qz)) + phi[j]);
+            const double cim = 2.0 * kPi * (beta * xer * qz);
+            double am = cre * v.hdr->rho;
+            double dpv = S.ex.inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+            if (status) { am = NAN; dpv = NAN; }
+            const int64_t o = gd.out_rr + ((int64_t)f * R + j) * R + i;
+            out.am[o] = am;
+            out.dp[o] = dpv;
+            if (i == j) {
+                const int64_t o1 = gd.out_r + (int64_t)f * R + j;
+                double ph = S.ex.inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xei, xer) - hankel0_angle(m0 * g.a[M - 1]);
+                double fo = excitation_force(dpv, m0, g.h, kRhoDefault);
+                if (status) { ph = NAN; fo = NAN; }
+                out.force[o1] = fo;
+                out.phase[o1] = ph;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // dense path: the reference's N_T x N_T complex system, one CTA (512 threads) per (geometry, frequency)
 template <int NB>
 __global__ void __launch_bounds__(512, 1) k_dense(const void* blob, void* ws, OutPtrs out) {
@@ -1535,6 +1684,7 @@ struct meemb200_plan {
     MeemPlanInfo info;
     std::vector<GeomDesc> geoms;
     int n_slots_geom, n_slots_work, geom_threads;
+    bool use_small;         // frequency stage by k_freq_small (one warp per system): N, K <= 16, R <= 4, no X output
     int gemm_flags;         // k_freq_gemm: bit 0 = rectangular-tile P = W^T W instead of the warp-tile-queue SYRK (tuning / tests)
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
@@ -1694,6 +1844,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = getenv("MEEMB200_NO_SYRK") ? 1 : 0;
+    P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
+                   !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
     P->solve_variant = (fits && P->smem_chol <= 44 * 1024) ? 1 : 0;
     if (const char* ev = getenv("MEEMB200_SOLVE_VARIANT")) {      // tuning / test override
@@ -1790,7 +1942,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
-    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? 6 + 2 * P->n_waves : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
+    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
     *out = P;
@@ -1843,7 +1995,27 @@ template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* i
 template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(k_freq_lu<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_freq);
     if (e != cudaSuccess) return e;
-    if (P->algo == MEEMB200_ALGO_SCHUR) {
+    if (P->algo == MEEMB200_ALGO_SCHUR && P->use_small) {
+        const size_t smem_small = sizeof(SmallWs) * kSmallWarps;
+        e = cudaFuncSetAttribute(k_freq_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_small);
+        if (e != cudaSuccess) return e;
+        if (!P->solve_grid) {
+            int per_sm = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_freq_small, 32 * kSmallWarps, smem_small);
+            if (e != cudaSuccess) return e;
+            if (per_sm < 1) return cudaErrorInvalidConfiguration;
+            P->solve_grid = per_sm * P->ctx->sm_count;
+        }
+        const BlobHeader* h = P->hdr();
+        int* wave_counters = reinterpret_cast<int*>(static_cast<char*>(ws) + h->ws_counters + 256);
+        const int64_t n_sys = P->info.n_sys;
+        const int grid = (int)std::min<int64_t>((n_sys + kSmallWarps - 1) / kSmallWarps, P->solve_grid);
+        k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters);
+        cudaEventRecord(P->ev[3], s);
+        cudaEventRecord(P->ev[4], s);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    } else if (P->algo == MEEMB200_ALGO_SCHUR) {
         e = cudaFuncSetAttribute(k_freq_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
         if (e != cudaSuccess) return e;
         typedef void (*solve_fn)(const void*, void*, OutPtrs, int, int, int*);

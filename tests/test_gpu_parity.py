@@ -239,7 +239,8 @@ def test_geometry_sweep_c4_vs_oracle(ofb):
 
 
 @pytest.mark.parametrize("env", [{"MEEMB200_SOLVE_VARIANT": "0"}, {"MEEMB200_SOLVE_VARIANT": "1"}, {"MEEMB200_SOLVE_VARIANT": "2"},
-                                 {"MEEMB200_SOLVE_VARIANT": "3"}, {"MEEMB200_NO_HCHOL": "1"}],
+                                 {"MEEMB200_SOLVE_VARIANT": "3"}, {"MEEMB200_NO_HCHOL": "1"}, {"MEEMB200_NO_SMALL": "1"},
+                                 {"MEEMB200_NO_SMALL": "1", "MEEMB200_NO_SYRK": "1"}],
                          ids=lambda e: "-".join(f"{k[9:]}={v}" for k, v in e.items()))
 @pytest.mark.parametrize("name", sorted(META2))
 def test_schur_kernel_variants_vs_reference(ofb, monkeypatch, name, env):
