@@ -1238,11 +1238,17 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
 // (10^5 geometries x 64 omega at 16 modes per region) and the mini_bicylinder replica batch spend ~40 ns of SM time per
 // system here instead of a 256-thread CTA with 64 x 128 DMMA tiles per 16 x 16 system.
 constexpr int kSmallMax = 16, kSmallMaxR = 4, kSmallWarps = 4;
+constexpr int kSmallLdA = kSmallMax + 2 * kSmallMaxR + 1;   // 25: odd stride, conflict-free column reads
 struct SmallWs {
-    double Imk[kSmallMax][kSmallMax + 1];
+    union {                                     // the geometry's operand block (steps 1-2), then the Cholesky block (3-4)
+        double A[kSmallMax][kSmallLdA];
+        double Dg[kCholNB * (kCholNB + 1) + kCholNB];
+    };
+    union {                                     // coupling table (steps 1-3), then the inverse factor (4-6)
+        double Imk[kSmallMax][kSmallMax + 1];
+        double Li[kCholNB * kCholLdP];
+    };
     double T[kSmallMax][kSmallMax + 1];
-    double Dg[kCholNB * (kCholNB + 1) + kCholNB];
-    double Li[kCholNB * kCholLdP];
     double aug[2 * kSmallMaxR][kSmallMax];      // rows r_i then q_j; overwritten by their forward-solved forms
     double ext[kSmallMax];
     Exterior ex;
@@ -1250,7 +1256,7 @@ struct SmallWs {
     int fail;
 };
 
-__global__ void __launch_bounds__(32 * kSmallWarps) k_freq_small(const void* blob, void* ws, OutPtrs out, int n_items, int* counter) {
+__global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* blob, void* ws, OutPtrs out, int n_items, int* counter) {
     extern __shared__ __align__(16) unsigned char smem[];
     DevView v = make_view(blob, ws);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1282,11 +1288,73 @@ __global__ void __launch_bounds__(32 * kSmallWarps) k_freq_small(const void* blo
         const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
         __syncwarp();
         if (lane == 0) { make_exterior(g, m0, S.ex); S.fail = 0; }
+        // the geometry's operand block into shared memory (coalesced, one latency): LA (factorised H) or HT
+        const int rows_out = (lmode ? hrank : N) + 2 * R;
+        {
+            const double* Ag = lmode ? LA : HT;
+            for (int e = lane; e < N * ldn; e += 32) {
+                const int k = e / ldn, m = e - k * ldn;
+                if (m < rows_out) S.A[k][m] = Ag[e];
+            }
+        }
         __syncwarp();
-        // 1. coupling table (reference-ordered imk for every entry), exterior diagonal; column order kp = k - 1, k = 0 last
-        for (int e = lane; e < N * K; e += 32) {
-            const int kk = e / K, kp = e - kk * K;
-            S.Imk[kk][kp] = imk(lmode ? perm[kk] : kk, (kp == K - 1) ? 0 : kp + 1, g, S.ex, mk, Nk);
+        // 1. coupling table, column order kp = k - 1, k = 0 last.  Interior entries by the angle-addition form of
+        // k_freq_gemm (2K + 2N sines / cosines tabulated per system, sinc series near a resonance); the row of harmonic 0
+        // and the column k = 0 through the reference-ordered imk()
+        if (!S.ex.inf_m0 && K > 1) {
+            double* tb = &S.T[0][0];                          // T is not live yet
+            double *tmk = tb, *tsk = tb + 16, *tck = tb + 32, *tnk = tb + 48, *tlm = tb + 64, *tsl = tb + 80, *tcl = tb + 96;
+            const double Lh = g.h - g.d[M - 1];
+            {
+                const bool isk = lane < 16;
+                const int idx = isk ? lane : lane - 16;
+                if (isk ? (idx < K) : (idx < N)) {
+                    const double val = isk ? mk[(idx == K - 1) ? 0 : idx + 1] : lambda_ni(lmode ? perm[idx] : idx, M - 1, g);
+                    double sv, cv;
+                    const double pr = val * Lh, er = fma(val, Lh, -pr);     // exact product = pr + er
+                    sincos(pr, &sv, &cv);
+                    if (isk) { tmk[idx] = val; tsk[idx] = fma(er, cv, sv); tck[idx] = fma(-er, sv, cv);
+                               tnk[idx] = sqrt(2.0 / Nk[(idx == K - 1) ? 0 : idx + 1]) * 0.5; }
+                    else { tlm[idx] = val; tsl[idx] = fma(er, cv, sv); tcl[idx] = fma(-er, sv, cv); }
+                }
+            }
+            const unsigned zmask = __ballot_sync(0xffffffffu, lane < N && (lmode ? perm[lane] : lane) == 0);
+            const int row0 = __ffs(zmask) - 1;
+            __syncwarp();
+            for (int e = lane; e < N + K - 1; e += 32) {
+                if (e < N) S.Imk[e][K - 1] = imk(lmode ? perm[e] : e, 0, g, S.ex, mk, Nk);
+                else S.Imk[row0][e - N] = imk(0, e - N + 1, g, S.ex, mk, Nk);
+            }
+            for (int e = lane; e < N * (K - 1); e += 32) {
+                const int n = e / (K - 1), kp = e - n * (K - 1);
+                if (n == row0) continue;
+                const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
+                const double mv = tmk[kp];
+                const double a = tsk[kp] * cl, b = tck[kp] * sl;
+                const double sp = mv + lam, sd = mv - lam;
+                const double x = sd * Lh, x2 = x * x;
+                double Ssin = a - b;
+                if (fabs(x) < 1.0) {
+                    double pl = -8.22063524662432972e-18;                       // -1/19!
+                    pl = fma(pl, x2, 2.81145725434552076e-15);                  //  1/17!
+                    pl = fma(pl, x2, -7.64716373181981648e-13);                 // -1/15!
+                    pl = fma(pl, x2, 1.60590438368216146e-10);                  //  1/13!
+                    pl = fma(pl, x2, -2.50521083854417188e-08);                 // -1/11!
+                    pl = fma(pl, x2, 2.75573192239858907e-06);                  //  1/9!
+                    pl = fma(pl, x2, -1.98412698412698413e-04);                 // -1/7!
+                    pl = fma(pl, x2, 8.33333333333333333e-03);                  //  1/5!
+                    pl = fma(pl, x2, -1.66666666666666667e-01);                 // -1/3!
+                    Ssin = fma(x * x2, pl, x);
+                }
+                double val = tnk[kp] * (fma(a + b, sd, Ssin * sp) / (sp * sd));
+                if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
+                S.Imk[n][kp] = val;
+            }
+        } else {
+            for (int e = lane; e < N * K; e += 32) {
+                const int kk = e / K, kp = e - kk * K;
+                S.Imk[kk][kp] = imk(lmode ? perm[kk] : kk, (kp == K - 1) ? 0 : kp + 1, g, S.ex, mk, Nk);
+            }
         }
         if (lane < K) {
             const cplx dg = ext_diag((lane == K - 1) ? 0 : lane + 1, g, S.ex, mk);
@@ -1295,13 +1363,11 @@ __global__ void __launch_bounds__(32 * kSmallWarps) k_freq_small(const void* blo
         }
         __syncwarp();
         // 2. [-r_i ; q_j ; W] (factorised H) or [T ; -r_i ; q_j] (H itself): out[m][n] = sum_k A[k][m] Imk[k][n]
-        const double* A = lmode ? LA : HT;
         const int nrow_t = lmode ? hrank : N;                 // rows of T / W
-        const int rows_out = nrow_t + 2 * R;
         for (int e = lane; e < rows_out * K; e += 32) {
             const int m = e / K, n = e - m * K;
             double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc = fma(A[(int64_t)k * ldn + m], S.Imk[k][n], acc);
+            for (int k = 0; k < N; ++k) acc = fma(S.A[k][m], S.Imk[k][n], acc);
             int a = -1, trow = -1;                            // destination: aug row a (sign) or T row
             if (lmode) { if (m < 2 * R) a = m; else trow = m - 2 * R; }
             else { if (m < N) trow = m; else a = m - N; }
