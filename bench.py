@@ -322,6 +322,8 @@ def main():
                 traffic = json.load(fh).get(args.workload, {}).get(kname, {}).get("dram_bytes_per_launch")
         except Exception:
             pass
+        if traffic is not None and not np.isfinite(traffic):
+            traffic = None
         roofline = {"bound": "tensor", "pipe": "FP64 DMMA (mma.sync m8n8k4 f64; tcgen05 has no FP64 kind)", "kernel": kname,
                     "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                     "peak_source": "measured in this run: max(DFMA register loop %.1f, DMMA m8n8k4 %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"

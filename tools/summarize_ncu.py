@@ -52,7 +52,8 @@ def main():
             v, u = vals.get(key, (0.0, "byte"))
             return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
         dram = to_bytes("dram__bytes_read.sum") + to_bytes("dram__bytes_write.sum")
-        summ.setdefault(workload, {})[KNAME.get(name, name)] = {"dram_bytes_per_launch": dram, "source": os.path.basename(rep), "tag": tag}
+        if dram == dram and abs(dram) != float("inf"):      # kernels ncu could not replay report NaN: keep them out of the JSON
+            summ.setdefault(workload, {})[KNAME.get(name, name)] = {"dram_bytes_per_launch": dram, "source": os.path.basename(rep), "tag": tag}
     with open(os.path.join(ROOT, "profiles", f"{tag}_ncu_summary.txt"), "w") as fh:
         fh.write("\n".join(out) + "\n")
     with open(summ_path, "w") as fh:
