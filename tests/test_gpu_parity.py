@@ -289,3 +289,24 @@ def test_mode_count_convergence_sweep_c5(ofb, geom):
     # convergence itself (size-independent property): the finest two finite levels agree to 3 digits
     fin = [r["added_mass"][:, 0, 0] for r in res if np.all(r["status"] == 0)]
     assert np.max(np.abs(fin[-1] - fin[-2]) / np.abs(fin[-1])) < 1e-3
+
+
+@pytest.mark.parametrize("M", [12, 24])
+def test_many_region_staircase_vs_oracle(ofb, M):
+    """SURVEY 8f rank 4 (slant-discretised bodies, dev/python/slants/helpers.py:80-125): a cone approximated by a staircase of
+    M regions - one body, all regions heaving - plus an overhanging variant (depth increasing outwards over the last third).
+    The device solves it with the same kernels (dense pivoted LU of the p x p block, p up to 376), not yet with a
+    block-bidiagonal elimination; parity bar unchanged."""
+    h, a_out, n = 10.0, 6.0, 8
+    a = [a_out * (i + 1) / M for i in range(M)]
+    d_cone = [6.0 - 5.0 * (i + 0.5) / M for i in range(M)]                       # depth decreasing outwards (case 1 everywhere)
+    d_over = [x if i < 2 * M // 3 else d_cone[2 * M // 3 - 1] + 0.05 * (i - 2 * M // 3 + 1) for i, x in enumerate(d_cone)]
+    om = np.array([0.6, 1.4, 2.2])
+    for d in (d_cone, d_over):
+        og = mo.FlatGeometry(h, a, d, [n] * (M + 1))
+        ref = mo.run_sweep(og, om, [0] * M, [0])
+        geo = ofb.FlatGeometry.from_body_map(h, a, d, [n] * (M + 1), [0] * M, [0])
+        for algo in (ofb.ALGO_SCHUR, ofb.ALGO_DENSE):
+            res = ofb.solve_batch([geo], om, algo=algo)[0]
+            assert np.all(res["status"] == 0)
+            _check(res, ref)
