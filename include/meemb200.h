@@ -172,6 +172,13 @@ int meemb200_last_timing(meemb200_plan* plan, float ms[5]);
  * Synchronises the stream.  Measurement only. */
 int meemb200_phase_profile(meemb200_plan* plan, const void* d_workspace, double cycles[16], void* stream);
 
+/* Host-side view of two device layouts (pure integer functions, no device needed; used by the CPU tests):
+ * kind 0: out[r] = offset (doubles) of row r of the packed lower-triangular system matrix for r = 0..n, out[n+1] = padded
+ *         size of the K = n triangle;
+ * kind 1: warp-tile list of the symmetric rank update for n columns: out[0] = tiles, then per tile
+ *         (group a, group b, first row block, row blocks, first column block, column blocks), largest tile first. */
+int meemb200_debug_layout(int kind, int n, int* out, int out_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,6 +54,7 @@ EXPORTS = [
     "meemb200_plan_create", "meemb200_plan_destroy", "meemb200_plan_info", "meemb200_plan_blob",
     "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_solve", "meemb200_solve_host",
     "meemb200_assemble", "meemb200_fields", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
+    "meemb200_debug_layout",
 ]
 
 

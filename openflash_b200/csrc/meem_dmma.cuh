@@ -203,6 +203,28 @@ __host__ __device__ inline bool syrk_fits(int Nc) {
     return kGemmStages * kSyrkKC * syrk_lds(Nc) <= kGemmSmemDoubles && ng * (ng + 1) / 2 <= kSyrkMaxTiles;
 }
 
+// Tile list of the lower triangle of an nb x nb block matrix: block groups of <= 4 (even split), tiles (a >= b), sorted by
+// the number of 8x8 blocks they compute (diagonal tiles: triangular), largest first.  Sets plan.nt, not plan.nb.
+__host__ __device__ inline void syrk_build_plan(SyrkPlan& plan, int nb) {
+    const int ng = (nb + 3) >> 2;
+    int nt = 0;
+    for (int a = 0; a < ng; ++a)
+        for (int b = 0; b <= a; ++b) {
+            const int ga = (a + 1) * nb / ng - a * nb / ng, gb = (b + 1) * nb / ng - b * nb / ng;
+            const int sz = (a == b) ? ga * (ga + 1) / 2 : ga * gb;
+            int pos = nt++;
+            while (pos > 0) {            // insertion sort, largest first
+                const int pa = plan.ta[pos - 1], pb = plan.tb[pos - 1];
+                const int qa = (pa + 1) * nb / ng - pa * nb / ng, qb = (pb + 1) * nb / ng - pb * nb / ng;
+                const int psz = (pa == pb) ? qa * (qa + 1) / 2 : qa * qb;
+                if (psz >= sz) break;
+                plan.ta[pos] = (unsigned char)pa; plan.tb[pos] = (unsigned char)pb; --pos;
+            }
+            plan.ta[pos] = (unsigned char)a; plan.tb[pos] = (unsigned char)b;
+        }
+    plan.nt = nt;
+}
+
 template <int NI, int NJ>
 __device__ __forceinline__ void syrk_chunk(const double* As, const double* Bs, int ld, int lc, double (&acc)[4][4][2]) {
 #pragma unroll
@@ -255,24 +277,7 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
     const int nchunk = (Kd + kSyrkKC - 1) / kSyrkKC;
     __syncthreads();
     if (plan.nb != nb) {                         // (re)build the sorted tile list: once per CTA for a uniform batch
-        if (threadIdx.x == 0) {
-            int nt = 0;
-            for (int a = 0; a < ng; ++a)
-                for (int b = 0; b <= a; ++b) {
-                    const int ga = (a + 1) * nb / ng - a * nb / ng, gb = (b + 1) * nb / ng - b * nb / ng;
-                    const int sz = (a == b) ? ga * (ga + 1) / 2 : ga * gb;
-                    int pos = nt++;
-                    while (pos > 0) {            // insertion sort, largest first
-                        const int pa = plan.ta[pos - 1], pb = plan.tb[pos - 1];
-                        const int qa = (pa + 1) * nb / ng - pa * nb / ng, qb = (pb + 1) * nb / ng - pb * nb / ng;
-                        const int psz = (pa == pb) ? qa * (qa + 1) / 2 : qa * qb;
-                        if (psz >= sz) break;
-                        plan.ta[pos] = pa; plan.tb[pos] = pb; --pos;
-                    }
-                    plan.ta[pos] = (unsigned char)a; plan.tb[pos] = (unsigned char)b;
-                }
-            plan.nt = nt;
-        }
+        if (threadIdx.x == 0) syrk_build_plan(plan, nb);
         __syncthreads();
         if (threadIdx.x == 0) plan.nb = nb;
     }

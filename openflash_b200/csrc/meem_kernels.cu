@@ -2186,6 +2186,34 @@ extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[5]) {
     return MEEMB200_OK;
 }
 
+// Host-side view of two device layouts, for the CPU tests (pure integer functions, no device needed):
+// kind 0: out[r] = tri_off(r) for r = 0 .. n, out[n + 1] = tri_doubles(n);  kind 1: SYRK warp-tile list for Nc = n columns:
+// out[0] = number of tiles, then (a, b, first row block, row blocks, first column block, column blocks) per tile.
+extern "C" int meemb200_debug_layout(int kind, int n, int* out, int out_len) {
+    if (!out || n < 1) return fail(MEEMB200_EINVAL, "bad argument");
+    if (kind == 0) {
+        if (out_len < n + 2) return fail(MEEMB200_EINVAL, "output too short");
+        for (int r = 0; r <= n; ++r) out[r] = tri_off(r);
+        out[n + 1] = tri_doubles(n);
+        return MEEMB200_OK;
+    }
+    if (kind == 1) {
+        if (!syrk_fits(n)) return fail(MEEMB200_EINVAL, "SYRK tile list does not apply to this width");
+        SyrkPlan plan;
+        const int nb = (n + 7) >> 3, ng = (nb + 3) >> 2;
+        syrk_build_plan(plan, nb);
+        if (out_len < 1 + 6 * plan.nt) return fail(MEEMB200_EINVAL, "output too short");
+        out[0] = plan.nt;
+        for (int t = 0; t < plan.nt; ++t) {
+            const int a = plan.ta[t], b = plan.tb[t];
+            int* o = out + 1 + 6 * t;
+            o[0] = a; o[1] = b; o[2] = a * nb / ng; o[3] = (a + 1) * nb / ng - o[2]; o[4] = b * nb / ng; o[5] = (b + 1) * nb / ng - o[4];
+        }
+        return MEEMB200_OK;
+    }
+    return fail(MEEMB200_EINVAL, "unknown kind");
+}
+
 extern "C" int meemb200_phase_profile(meemb200_plan* P, const void* d_ws, double cycles[16], void* stream) {
     if (!P || !d_ws || !cycles) return fail(MEEMB200_EINVAL, "NULL argument");
     unsigned long long raw[16];

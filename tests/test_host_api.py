@@ -116,3 +116,38 @@ def test_results_container_shapes():
     res.store_potential_coefficients(X, [4, 4, 4])
     pr = ds["potentials_real"].values
     assert pr.shape == (F, R, 3, 8) and np.isnan(pr[0, 0, 0, 4]) and pr[0, 0, 1, 7] == 11.0 and pr[0, 0, 2, 0] == 12.0
+
+
+def test_packed_triangle_and_syrk_tile_layouts():
+    """Host view of two device layouts (meemb200_debug_layout; integer functions only, no GPU): the packed lower-triangular
+    system matrix of k_freq_solve / k_hchol and the warp-tile list of the symmetric rank update in k_freq_gemm."""
+    lib = _lib.load()
+    lib.meemb200_debug_layout.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    for K in (1, 2, 7, 10, 16, 50, 199, 200, 400):
+        out = (ctypes.c_int * (K + 2))()
+        assert lib.meemb200_debug_layout(0, K, out, K + 2) == 0
+        off = np.array(out[:K + 1])
+        assert off[0] == 0 and np.all(off % 2 == 0)                       # 16-byte aligned rows (double2 accesses)
+        assert np.all(np.diff(off) >= np.arange(K) + 1)                    # row r holds its r + 1 entries without overlap
+        assert np.all(np.diff(off) <= np.arange(K) + 2)                    # ... with at most one padding slot
+        assert out[K + 1] >= off[K] and out[K + 1] % 8 == 0 and out[K + 1] - off[K] < 8
+    for Nc in (64, 100, 199, 200, 256):
+        buf = (ctypes.c_int * (1 + 6 * 96))()
+        assert lib.meemb200_debug_layout(1, Nc, buf, len(buf)) == 0
+        nt, nb = buf[0], (Nc + 7) // 8
+        tiles = np.array(buf[1:1 + 6 * nt]).reshape(nt, 6)
+        cover = np.zeros((nb, nb), int)
+        sizes = []
+        for a, b, r0, nr, c0, nc in tiles:
+            assert 1 <= nr <= 4 and 1 <= nc <= 4 and a >= b
+            if a == b:
+                assert (r0, nr) == (c0, nc)
+                for i in range(nr):
+                    cover[r0 + i, c0:c0 + i + 1] += 1                      # diagonal tiles compute their lower blocks only
+                sizes.append(nr * (nr + 1) // 2)
+            else:
+                cover[r0:r0 + nr, c0:c0 + nc] += 1
+                sizes.append(nr * nc)
+        assert np.array_equal(cover, np.tril(np.ones((nb, nb), int)))      # every lower block exactly once, nothing above
+        assert sizes == sorted(sizes, reverse=True)                        # largest first: balanced passes of 8 warps
+    assert lib.meemb200_debug_layout(1, 1000, buf, len(buf)) != 0          # too wide for the staged SYRK: refused, not garbage
