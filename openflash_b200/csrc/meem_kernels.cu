@@ -486,7 +486,7 @@ struct GemmSmem {
 // radial derivative vanishes) go to the end of the permutation; the remaining block is well conditioned (smallest /
 // largest eigenvalue >= 4e-3 over every geometry probed), so no pivoting is needed.  Any non-positive pivot or negative
 // diagonal marks the geometry as not factorised and the frequency stage uses H itself.
-constexpr int kHcholThreads = 256;
+constexpr int kHcholThreads = 512;          // maximum; small geometries launch 128
 __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void* ws, unsigned smem_limit) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double red_v[kHcholThreads / 32];
@@ -1751,6 +1751,7 @@ struct meemb200_plan {
     std::vector<GeomDesc> geoms;
     int n_slots_geom, n_slots_work, geom_threads;
     bool use_small;         // frequency stage by k_freq_small (one warp per system): N, K <= 16, R <= 4, no X output
+    int max_N;
     int gemm_flags;         // k_freq_gemm: bit 0 = rectangular-tile P = W^T W instead of the warp-tile-queue SYRK (tuning / tests)
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
@@ -1907,6 +1908,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     // Resident by default only while >= 5 CTAs still fit an SM (K <~ 75): the factorisation is a latency chain (13 panels
     // at K = 200, each with a 16-step register Cholesky) that is hidden by CTAs in flight, not by threads per CTA -
     // measured on big_tricylinder: L2-resident 5 CTAs/SM 2.9 ms, shared-memory-resident 1 CTA/SM x 512 threads 3.0 ms.
+    P->max_N = max_N;
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = getenv("MEEMB200_NO_SYRK") ? 1 : 0;
@@ -2158,7 +2160,8 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
         CUDA_TRY(P->nb_geom == 8 ? launch_geom<8>(P, d_in, d_ws, s) : P->nb_geom == 4 ? launch_geom<4>(P, d_in, d_ws, s) : launch_geom<2>(P, d_in, d_ws, s));
         if (h->algo == MEEMB200_ALGO_SCHUR) {
             CUDA_TRY(cudaFuncSetAttribute(k_hchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(P->smem_hchol, 1024)));
-            k_hchol<<<std::min(h->n_geom, 8 * P->ctx->sm_count), kHcholThreads, std::max<size_t>(P->smem_hchol, 1024), s>>>(d_in, d_ws, (unsigned)P->smem_hchol);
+            const int hthreads = P->max_N > 64 ? kHcholThreads : 128;
+            k_hchol<<<std::min(h->n_geom, 8 * P->ctx->sm_count), hthreads, std::max<size_t>(P->smem_hchol, 1024), s>>>(d_in, d_ws, (unsigned)P->smem_hchol);
             CUDA_TRY(cudaGetLastError());
         }
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
