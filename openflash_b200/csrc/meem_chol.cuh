@@ -165,28 +165,45 @@ __device__ void cta_cholesky(const TriMat P, int naug, double* sm, int* fail, lo
         if (ncol <= 0) continue;
         // trailing update on the DMMA pipe: 16 x 32 warp tiles of the lower triangle, C tile is the accumulator
         const int ntr = prow / 16, ntc = (ncol + 31) / 32;
-        for (int t = warp; t < ntr * ntc; t += nwarp) {
-            const int ti = t / ntc, tj = t - ti * ntc;
-            const int ri0 = ti * 16, cj0 = tj * 32;
-            if (cj0 > ri0 + 15 || ri0 >= nrow) continue;
+        // only tiles that touch the lower triangle, dealt round-robin to the warps (a strided walk over the full ntr x ntc
+        // grid with skips left the warps up to 20 % out of balance)
+        int tcount = 0;
+        for (int ti = 0; ti < ntr; ++ti) {
+          const int ri0 = ti * 16;
+          if (ri0 >= nrow) break;
+          const int ntj = min(ntc, (ri0 + 15) / 32 + 1);
+          for (int tj = 0; tj < ntj; ++tj) {
+            if ((tcount++ % nwarp) != warp) continue;
+            const int cj0 = tj * 32;
             double acc[2][4][2];
+            // the lane's two row pointers once per tile (tri_off is ~10 integer instructions: 16 evaluations per tile before)
+            double* rp[2];
+            int rlim[2];                                  // columns c <= rlim are stored for that row (-1: row out of range)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int r = ri0 + 8 * i + lr;
+                rp[i] = P.row(kb + min(r, nrow - 1)) + kb;
+                rlim[i] = (r < nrow) ? min(r, ncol - 1) : -1;
+            }
+            const int cbase = cj0 + 2 * lc;
 #pragma unroll
             for (int i = 0; i < 2; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
+                    const int c = cbase + 8 * j;
                     double2 v = make_double2(0.0, 0.0);
-                    if (r < nrow && c <= r && c < ncol)
-                        v = *reinterpret_cast<const double2*>(P.row(kb + r) + kb + c);
+                    if (c <= rlim[i]) v = *reinterpret_cast<const double2*>(rp[i] + c);
                     acc[i][j][0] = v.x; acc[i][j][1] = v.y;
                 }
+            const double* pa = Pn + (ri0 + lr) * kCholLdP + lc;
+            const double* pb = Pn + (cj0 + lr) * kCholLdP + lc;
 #pragma unroll
             for (int ks = 0; ks < kCholNB / 4; ++ks) {
                 double af[2], bf[4];
 #pragma unroll
-                for (int i = 0; i < 2; ++i) af[i] = -Pn[(ri0 + 8 * i + lr) * kCholLdP + ks * 4 + lc];
+                for (int i = 0; i < 2; ++i) af[i] = -pa[8 * i * kCholLdP + ks * 4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) bf[j] = Pn[(cj0 + 8 * j + lr) * kCholLdP + ks * 4 + lc];
+                for (int j = 0; j < 4; ++j) bf[j] = pb[8 * j * kCholLdP + ks * 4];
 #pragma unroll
                 for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -196,15 +213,161 @@ __device__ void cta_cholesky(const TriMat P, int naug, double* sm, int* fail, lo
             for (int i = 0; i < 2; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const int r = ri0 + 8 * i + lr, c = cj0 + 8 * j + 2 * lc;
-                    if (r < nrow && c <= r && c < ncol)
-                        *reinterpret_cast<double2*>(P.row(kb + r) + kb + c) = make_double2(acc[i][j][0], acc[i][j][1]);
+                    const int c = cbase + 8 * j;
+                    if (c <= rlim[i]) *reinterpret_cast<double2*>(rp[i] + c) = make_double2(acc[i][j][0], acc[i][j][1]);
                 }
+          }
         }
 #ifdef MEEM_CHOL_PROF
         __syncthreads();
         CHOL_T(3);
 #endif
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// LEFT-LOOKING variant for a matrix that lives in L2 / HBM: block column j is formed as
+//   C_j = P[:, j] - L[:, 0:j] L[j, 0:j]^T
+// with the accumulators in registers over the whole contraction (the 16 pivot rows L[j, 0:j] staged in shared memory, the
+// other operand streamed from L2 with independent, prefetchable loads), then factorised / solved and written ONCE.  The
+// right-looking form above reads and writes the whole trailing triangle at every one of the K / 16 steps, each tile a
+// dependent L2 round trip; this one reads K^3 / 96 doubles per system and writes the factor once.
+// Shared memory: Dg | Li as above, then Lrow[16][ldr], ldr = chol_ll_ldr(K).  Same result layout as cta_cholesky.
+__host__ __device__ inline int chol_ll_ldr(int K) { const int n8 = (K + 7) & ~7; return n8 + ((n8 & 15) ? 12 : 4); }
+__host__ __device__ inline size_t chol_ll_smem_bytes(int K) {
+    return sizeof(double) * ((size_t)kCholNB * (kCholNB + 1) + kCholNB + (size_t)kCholNB * kCholLdP + (size_t)kCholNB * chol_ll_ldr(K));
+}
+
+// C blocks (8 rows x 16 columns each) of NBLK row blocks row0 + u * rstride against the staged pivot rows:
+// acc[u][j][e] = C_u[lr][8 j + 2 lc + e].  The NBLK operand streams are independent, so 4 NBLK L2 loads are in flight per
+// lane (unroll 4); from_smem: the rows ARE the staged pivot rows (diagonal block), read them from shared memory.
+template <int NBLK>
+__device__ __forceinline__ void chol_ll_blocks(const TriMat& P, int row0, int rstride, int KR, int k0, int nb, bool diag,
+                                               const double* Lrow, int ldr, int lr, int lc, double (&acc)[NBLK][2][2]) {
+    const double* pa[NBLK];
+    bool rok[NBLK];
+#pragma unroll
+    for (int u = 0; u < NBLK; ++u) {
+        const int row = row0 + u * rstride + lr;
+        rok[u] = row < KR;
+        const double* rp = P.row(rok[u] ? row : KR - 1);
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int c = 8 * j + 2 * lc + e;
+                const bool ok = rok[u] && c < nb && (!diag || k0 + c <= row);
+                acc[u][j][e] = ok ? rp[k0 + c] : 0.0;
+            }
+        pa[u] = diag ? Lrow + (row - k0) * ldr + lc : rp + lc;
+        if (diag && !rok[u]) pa[u] = Lrow + lc;
+    }
+    const double* pb = Lrow + lr * ldr + lc;
+#pragma unroll 4
+    for (int ks = 0; ks < (k0 >> 2); ++ks) {
+        double a[NBLK];
+#pragma unroll
+        for (int u = 0; u < NBLK; ++u) a[u] = rok[u] ? -pa[u][4 * ks] : 0.0;
+        const double b0 = pb[4 * ks], b1 = pb[8 * ldr + 4 * ks];
+#pragma unroll
+        for (int u = 0; u < NBLK; ++u) {
+            dmma(acc[u][0][0], acc[u][0][1], a[u], b0);
+            dmma(acc[u][1][0], acc[u][1][1], a[u], b1);
+        }
+    }
+}
+
+// L21 block = C block Linv^T (the C fragments re-laid out by shuffles), stored once
+__device__ __forceinline__ void chol_ll_solve_store(const TriMat& P, int row0, int KR, int k0, int nb, const double (&bf)[kCholNB / 4][2],
+                                                    int lane, const double (&acc)[2][2]) {
+    const int lr = lane >> 2, lc = lane & 3;
+    double out[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+    for (int ks = 0; ks < kCholNB / 4; ++ks) {
+        // A fragment a = C[lr][4 ks + lc] sits in lane (lr, 2 (ks & 1) + (lc >> 1)) as acc[ks >> 1][lc & 1]
+        const int src = (lane & ~3) | (2 * (ks & 1) + (lc >> 1));
+        const double v0 = __shfl_sync(0xffffffffu, acc[ks >> 1][0], src);
+        const double v1 = __shfl_sync(0xffffffffu, acc[ks >> 1][1], src);
+        const double a = (lc & 1) ? v1 : v0;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) dmma(out[j][0], out[j][1], a, bf[ks][j]);
+    }
+    const int row = row0 + lr;
+    if (row < KR) {
+        double* rp = P.row(row) + k0;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int c = 8 * j + 2 * lc;
+            if (c + 1 < nb) *reinterpret_cast<double2*>(rp + c) = make_double2(out[j][0], out[j][1]);
+            else if (c < nb) rp[c] = out[j][0];
+        }
+    }
+}
+
+__device__ void cta_cholesky_ll(const TriMat P, int naug, double* sm, int* fail) {
+    const int K = P.K;
+    double* Dg = sm;
+    double* Li = Dg + kCholNB * (kCholNB + 1) + kCholNB;
+    double* Lrow = Li + kCholNB * kCholLdP;
+    const int ldr = chol_ll_ldr(K);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int KR = K + naug;
+    for (int k0 = 0; k0 < K; k0 += kCholNB) {
+        const int nb = min(kCholNB, K - k0);
+        const int kb = k0 + nb;
+        __syncthreads();                                   // previous column's readers of Lrow / Li are done
+        // pivot rows L[k0 .. k0+15][0 .. k0) -> shared memory (rows beyond nb: zeros)
+        for (int idx = tid; idx < kCholNB * (k0 >> 1); idx += nthr) {
+            const int i = idx / (k0 >> 1), g = idx - i * (k0 >> 1);
+            double2 v = make_double2(0.0, 0.0);
+            if (i < nb) v = *reinterpret_cast<const double2*>(P.row(k0 + i) + 2 * g);
+            *reinterpret_cast<double2*>(Lrow + i * ldr + 2 * g) = v;
+        }
+        __syncthreads();
+        // diagonal block: row blocks 0, 1 of the block column (lower triangle), identity-padded into Dg
+        for (int w = warp; w < 2; w += nwarp) {
+            double acc[1][2][2];
+            chol_ll_blocks<1>(P, k0 + 8 * w, 0, k0 + nb, k0, nb, true, Lrow, ldr, lr, lc, acc);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int i = 8 * w + lr, c = 8 * j + 2 * lc + e;
+                    Dg[i * (kCholNB + 1) + c] = (i < nb && c < nb) ? acc[0][j][e] : (i == c ? 1.0 : 0.0);
+                }
+        }
+        __syncthreads();
+        if (warp == 0) warp_chol16(Dg, Li, fail);
+        __syncthreads();
+        for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {      // the inverse of the factor block replaces the block
+            const int i = idx >> 4, c = idx & 15;
+            if (i < nb && c <= i) P.row(k0 + i)[k0 + c] = Li[i * kCholLdP + c];
+        }
+        const int nrow = KR - kb;
+        if (nrow <= 0) break;
+        // rows below: C block, then L21 = C Linv^T with the C fragments re-laid out by shuffles, stored once
+        double bf[kCholNB / 4][2];
+#pragma unroll
+        for (int ks = 0; ks < kCholNB / 4; ++ks)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) bf[ks][j] = Li[(8 * j + lr) * kCholLdP + ks * 4 + lc];
+        const int nrb = (nrow + 7) >> 3;
+        // two row blocks in flight per warp while whole pairs remain (8 independent L2 loads per lane), then singles
+        int rb = warp;
+        for (; rb + nwarp < nrb; rb += 2 * nwarp) {
+            double acc[2][2][2];
+            chol_ll_blocks<2>(P, kb + 8 * rb, 8 * nwarp, KR, k0, nb, false, Lrow, ldr, lr, lc, acc);
+            chol_ll_solve_store(P, kb + 8 * rb, KR, k0, nb, bf, lane, acc[0]);
+            chol_ll_solve_store(P, kb + 8 * (rb + nwarp), KR, k0, nb, bf, lane, acc[1]);
+        }
+        if (rb < nrb) {
+            double acc[1][2][2];
+            chol_ll_blocks<1>(P, kb + 8 * rb, 0, KR, k0, nb, false, Lrow, ldr, lr, lc, acc);
+            chol_ll_solve_store(P, kb + 8 * rb, KR, k0, nb, bf, lane, acc[0]);
+        }
     }
     __syncthreads();
 }

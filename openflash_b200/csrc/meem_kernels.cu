@@ -1039,7 +1039,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
 // factorisation / back-substitution runs there (K <= ~208 at one CTA per SM); otherwise P stays in its L2-resident buffer.
 #undef HARM
 template <int THREADS, int MINB, bool RESIDENT>
-__global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter) {
+__global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, void* ws, OutPtrs out, int item0, int item1, int* counter, int flags) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
@@ -1100,7 +1100,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
         cta_cholesky(P, 2 * R, sm, &sh_fail, tph);
         tprev = clock64();
 #else
-        cta_cholesky(P, 2 * R, sm, &sh_fail);
+        // P in L2: left-looking (one pass over the factor per block column, accumulators in registers); P in shared
+        // memory: right-looking
+        if (!RESIDENT && !(flags & 2)) cta_cholesky_ll(P, 2 * R, sm, &sh_fail);
+        else cta_cholesky(P, 2 * R, sm, &sh_fail);
         PHASE_END(0);
 #endif
         // 6. (X output only) back-substitution for [w_1 .. w_R, z],  z = P^{-1} e_last.  The diagonal blocks of P hold the
@@ -1752,7 +1755,8 @@ struct meemb200_plan {
     int n_slots_geom, n_slots_work, geom_threads;
     bool use_small;         // frequency stage by k_freq_small (one warp per system): N, K <= 16, R <= 4, no X output
     int max_N;
-    int gemm_flags;         // k_freq_gemm: bit 0 = rectangular-tile P = W^T W instead of the warp-tile-queue SYRK (tuning / tests)
+    int gemm_flags;         // bit 0: k_freq_gemm uses rectangular tiles for P = W^T W instead of the warp-tile-queue SYRK;
+                            // bit 1: k_freq_solve uses the right-looking Cholesky also when P lives in L2 (tuning / tests)
     int nb_geom, nb_freq, nb_dense;            // panel widths chosen from shared-memory limits
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
     int algo;
@@ -1911,7 +1915,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->max_N = max_N;
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
-    P->gemm_flags = getenv("MEEMB200_NO_SYRK") ? 1 : 0;
+    P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0);
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
@@ -2086,7 +2090,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
     } else if (P->algo == MEEMB200_ALGO_SCHUR) {
         e = cudaFuncSetAttribute(k_freq_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
         if (e != cudaSuccess) return e;
-        typedef void (*solve_fn)(const void*, void*, OutPtrs, int, int, int*);
+        typedef void (*solve_fn)(const void*, void*, OutPtrs, int, int, int*, int);
         static const solve_fn solve_k[4] = {k_freq_solve<128, 5, false>, k_freq_solve<128, 5, true>, k_freq_solve<256, 2, true>,
                                             k_freq_solve<512, 1, true>};
         static const int solve_thr[4] = {128, 128, 256, 512};
@@ -2109,7 +2113,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
             const int n = item1 - item0;
             k_freq_gemm<<<std::min(n, P->n_slots_work), 256, kGemmSmemBytes, s>>>(in, ws, item0, item1, wave_counters + 2 * w, P->gemm_flags);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[3], s);
-            ksolve<<<std::min(n, P->solve_grid), nthr_solve, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1);
+            ksolve<<<std::min(n, P->solve_grid), nthr_solve, P->smem_chol, s>>>(in, ws, o, item0, item1, wave_counters + 2 * w + 1, P->gemm_flags);
             if (w == P->n_waves - 1) cudaEventRecord(P->ev[4], s);
         }
         e = cudaGetLastError();
