@@ -340,13 +340,19 @@ __device__ void cta_cholesky_ll(const TriMat P, int naug, double* sm, int* fail)
                 }
         }
         __syncthreads();
+        // warp 0 factorises the diagonal block; meanwhile the other warps already form their first two C blocks each (these
+        // need the staged pivot rows only, not the factor) and hold them in registers across the barrier
+        const int nrow = KR - kb;
+        const int nrb = nrow > 0 ? (nrow + 7) >> 3 : 0;
+        const int nhelp = nwarp - 1;
+        double hacc[2][2][2];
         if (warp == 0) warp_chol16(Dg, Li, fail);
+        else if (warp - 1 < nrb) chol_ll_blocks<2>(P, kb + 8 * (warp - 1), 8 * nhelp, KR, k0, nb, false, Lrow, ldr, lr, lc, hacc);
         __syncthreads();
         for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr) {      // the inverse of the factor block replaces the block
             const int i = idx >> 4, c = idx & 15;
             if (i < nb && c <= i) P.row(k0 + i)[k0 + c] = Li[i * kCholLdP + c];
         }
-        const int nrow = KR - kb;
         if (nrow <= 0) break;
         // rows below: C block, then L21 = C Linv^T with the C fragments re-laid out by shuffles, stored once
         double bf[kCholNB / 4][2];
@@ -354,9 +360,13 @@ __device__ void cta_cholesky_ll(const TriMat P, int naug, double* sm, int* fail)
         for (int ks = 0; ks < kCholNB / 4; ++ks)
 #pragma unroll
             for (int j = 0; j < 2; ++j) bf[ks][j] = Li[(8 * j + lr) * kCholLdP + ks * 4 + lc];
-        const int nrb = (nrow + 7) >> 3;
+        if (warp > 0 && warp - 1 < nrb) {
+            chol_ll_solve_store(P, kb + 8 * (warp - 1), KR, k0, nb, bf, lane, hacc[0]);
+            if (warp - 1 + nhelp < nrb) chol_ll_solve_store(P, kb + 8 * (warp - 1 + nhelp), KR, k0, nb, bf, lane, hacc[1]);
+        }
+        const int rb_first = min(nrb, 2 * nhelp);            // row blocks [0, rb_first) are done
         // two row blocks in flight per warp while whole pairs remain (8 independent L2 loads per lane), then singles
-        int rb = warp;
+        int rb = rb_first + warp;
         for (; rb + nwarp < nrb; rb += 2 * nwarp) {
             double acc[2][2][2];
             chol_ll_blocks<2>(P, kb + 8 * rb, 8 * nwarp, KR, k0, nb, false, Lrow, ldr, lr, lc, acc);
