@@ -184,6 +184,23 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
 }
 
 
+// mbarrier + 1-D bulk copy (TMA unit, SASS UBLKCP): whole rows / whole matrices global -> shared with one instruction
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------------
 // Lower triangle of C = W^T W  (W: Kd x Nc row-major, leading dimension ldw), the symmetric rank-Kd update of the
 // factorised-H form of the frequency stage.  Unlike cta_gemm_dmma, whole-width chunks of W (kSyrkKC x Nc) are staged,
@@ -268,8 +285,24 @@ __device__ __forceinline__ void syrk_stage_load(double* st, int lds, const doubl
     }
 }
 
+// bars != nullptr: the chunks are brought in by the TMA unit - lane r of warp 0 issues ONE bulk copy for row r of the chunk
+// (16 instructions per chunk instead of ~1600 cp.async with their address arithmetic), completion through one mbarrier per
+// stage (phase: the caller's parity bits, one per stage).  Requires Nc % 8 == 0 and rows [Kd, pad16(Kd)) of W zero.
+__device__ __forceinline__ void syrk_stage_bulk(double* st, int lds, const double* W, int ldw, int n8, int k0, uint64_t* bar) {
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        if (lane == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // earlier generic-proxy accesses to this stage
+            mbar_expect_tx(bar, (unsigned)(kSyrkKC * n8 * sizeof(double)));
+        }
+        __syncwarp();
+        if (lane < kSyrkKC) bulk_g2s(st + lane * lds, W + (long)(k0 + lane) * ldw, (unsigned)(n8 * sizeof(double)), bar);
+    }
+}
+
 template <class Epi>
-__device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int Kd, double* sm, SyrkPlan& plan, Epi epi) {
+__device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int Kd, double* sm, SyrkPlan& plan,
+                              uint64_t* bars, unsigned& phase, Epi epi) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
     const int lr = lane >> 2, lc = lane & 3;
     const int nb = (Nc + 7) >> 3, n8 = nb * 8, lds = syrk_lds(Nc);
@@ -295,15 +328,26 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
         __syncthreads();      // previous users of the stage buffers are done
-        syrk_stage_load(sm, lds, W, ldw, n8, 0, Kd);
-        cp_async_commit();
-        if (1 < nchunk) syrk_stage_load(sm + kSyrkKC * lds, lds, W, ldw, n8, kSyrkKC, Kd);
-        cp_async_commit();
-        for (int c = 0; c < nchunk; ++c) {
-            cp_async_wait<1>();
-            __syncthreads();
-            if (c + 2 < nchunk) syrk_stage_load(sm + ((c + 2) % kGemmStages) * kSyrkKC * lds, lds, W, ldw, n8, (c + 2) * kSyrkKC, Kd);
+        if (bars) {
+            syrk_stage_bulk(sm, lds, W, ldw, n8, 0, &bars[0]);
+            if (1 < nchunk) syrk_stage_bulk(sm + kSyrkKC * lds, lds, W, ldw, n8, kSyrkKC, &bars[1]);
+        } else {
+            syrk_stage_load(sm, lds, W, ldw, n8, 0, Kd);
             cp_async_commit();
+            if (1 < nchunk) syrk_stage_load(sm + kSyrkKC * lds, lds, W, ldw, n8, kSyrkKC, Kd);
+            cp_async_commit();
+        }
+        for (int c = 0; c < nchunk; ++c) {
+            const int st_ = c % kGemmStages;
+            if (bars) { mbar_wait(&bars[st_], (phase >> st_) & 1u); phase ^= 1u << st_; }
+            else cp_async_wait<1>();
+            __syncthreads();
+            if (c + 2 < nchunk) {
+                const int s2 = (c + 2) % kGemmStages;
+                if (bars) syrk_stage_bulk(sm + s2 * kSyrkKC * lds, lds, W, ldw, n8, (c + 2) * kSyrkKC, &bars[s2]);
+                else syrk_stage_load(sm + s2 * kSyrkKC * lds, lds, W, ldw, n8, (c + 2) * kSyrkKC, Kd);
+            }
+            if (!bars) cp_async_commit();
             const double* cur = sm + (c % kGemmStages) * kSyrkKC * lds;
             const double* As = cur + rb0 * 8 + lr;
             const double* Bs = cur + cb0 * 8 + lr;

@@ -828,7 +828,10 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
 // The q_j ride through the factorisation as right-hand sides like the r_i: with P = L L^T, q_j . P^{-1} r_i =
 // (L^{-1} q_j) . (L^{-1} r_i), and everything the coefficients need from z = P^{-1} e_last is L_KK and (L^{-1} q_j)_K -
 // so the coefficient path has no back-substitution at all (only the optional X output does).
-__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * N * pad8(K) + 16; }
+// (rows padded to a multiple of 16 and kept zero beyond the live ones: the bulk-copied contraction chunks of the rank update
+// read whole 16-row chunks)
+__host__ __device__ inline int pad16(int n) { return (n + 15) & ~15; }
+__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * pad16(N) * pad8(K) + 16; }
 __host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)tri_doubles(K) + (int64_t)(3 * R + 2) * pad8(K) + 8; }
 // k_freq_solve dynamic shared memory: Cholesky scratch | xc, vv (X path) | [resident variant: Ptri | aug[R][ldk] | xs[R+1][ldk]]
 __host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N, bool want_x, bool resident) {
@@ -852,7 +855,14 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
     __shared__ Exterior ex;
     __shared__ int sh_item, sh_row0;
     __shared__ SyrkPlan sh_syrk;
-    if (threadIdx.x == 0) sh_syrk.nb = -1;
+    __shared__ __align__(8) uint64_t sh_mbar[kGemmStages];
+    unsigned mbar_phase = 0;                               // bit s: parity the next wait on stage s expects
+    if (threadIdx.x == 0) {
+        sh_syrk.nb = -1;
+        for (int i = 0; i < kGemmStages; ++i) mbar_init(&sh_mbar[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    const bool use_bulk = (flags & 4) == 0;
     const bool use_syrk = (flags & 1) == 0;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
@@ -876,7 +886,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         const int N = gd.N, K = gd.K, R = gd.R;
         const int ldk = pad8(K), ldn = gs_ldn(N, R);
         double* Imk = slot;
-        double* T = Imk + (int64_t)N * ldk;
+        double* T = Imk + (int64_t)pad16(N) * ldk;
         double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
         double* P = sys;                                   // packed lower triangle
         double* aug = P + tri_doubles(K);                  // [2R][ldk] right-hand sides r_i, then q_j
@@ -1008,7 +1018,17 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
                 *reinterpret_cast<double2*>(P + tri_off(m) + n) = make_double2(v0, v1);
             }
         };
-        if (lmode && use_syrk && K >= 64 && syrk_fits(K)) cta_syrk_dmma(T, ldk, K, hrank, sm, sh_syrk, store_p);
+        if (lmode && use_syrk && K >= 64 && syrk_fits(K)) {
+            const bool bulk = use_bulk && (K & 7) == 0;        // whole 64-byte rows: the bulk copies need 16-byte sizes
+            if (bulk) {
+                // rows [hrank, pad16(hrank)) of W are read by the last 16-row chunk: zero; then make this CTA's generic-proxy
+                // stores to W visible to the async proxy (TMA reads of global memory)
+                for (int e = tid; e < (pad16(hrank) - hrank) * ldk; e += nthr) T[(int64_t)hrank * ldk + e] = 0.0;
+                asm volatile("fence.proxy.async;" ::: "memory");
+                __syncthreads();
+            }
+            cta_syrk_dmma(T, ldk, K, hrank, sm, sh_syrk, bulk ? sh_mbar : nullptr, mbar_phase, store_p);
+        }
         else cta_gemm_dmma(lmode ? T : Imk, ldk, T, ldk, K, K, lmode ? hrank : N, true, -1, sm, store_p);
         PHASE_END(PH_GEMM2);
     }
@@ -1016,23 +1036,6 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         unsigned long long* prof = reinterpret_cast<unsigned long long*>(v.counters + 16);
         for (int i = 0; i < 4; ++i) atomicAdd(&prof[i], (unsigned long long)tph[i]);
     }
-}
-
-// mbarrier + 1-D bulk copy (TMA unit, SASS UBLKCP) used to bring a system's packed P into shared memory
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
-    asm volatile("{\n.reg .pred p;\nWAIT_%=:\n"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-                 "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
 }
 
 // RESIDENT: the packed P (+ right-hand-side rows) is pulled into shared memory with one bulk copy and the whole
@@ -1915,7 +1918,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->max_N = max_N;
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
-    P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0);
+    P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0);
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
