@@ -240,13 +240,15 @@ def test_geometry_sweep_c4_vs_oracle(ofb):
 
 @pytest.mark.parametrize("env", [{"MEEMB200_SOLVE_VARIANT": "0"}, {"MEEMB200_SOLVE_VARIANT": "1"}, {"MEEMB200_SOLVE_VARIANT": "2"},
                                  {"MEEMB200_SOLVE_VARIANT": "3"}, {"MEEMB200_NO_HCHOL": "1"}, {"MEEMB200_NO_SMALL": "1"},
-                                 {"MEEMB200_NO_SMALL": "1", "MEEMB200_NO_SYRK": "1"}],
+                                 {"MEEMB200_NO_SMALL": "1", "MEEMB200_NO_SYRK": "1"}, {"MEEMB200_NO_SMALL": "1", "MEEMB200_NO_BULK": "1"},
+                                 {"MEEMB200_NO_SMALL": "1", "MEEMB200_NO_LL": "1"}],
                          ids=lambda e: "-".join(f"{k[9:]}={v}" for k, v in e.items()))
 @pytest.mark.parametrize("name", sorted(META2))
 def test_schur_kernel_variants_vs_reference(ofb, monkeypatch, name, env):
-    """Every k_freq_solve variant (P in its L2 buffer / resident in shared memory at 128, 256, 512 threads) and the
-    unfactorised-H form of k_freq_gemm meet the same bar as the default path, X included (the overrides are read at plan
-    creation)."""
+    """Every k_freq_solve variant (P in its L2 buffer with the left- or right-looking Cholesky / resident in shared memory
+    at 128, 256, 512 threads), the unfactorised-H form of k_freq_gemm, its rank update with rectangular tiles, cp.async or TMA
+    bulk staging, and the CTA-per-system path for small systems meet the same bar as the default path, X included (the
+    overrides are read at plan creation)."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     s = META2[name]
