@@ -122,8 +122,11 @@ class Results:
         return self.dataset
 
     def export_to_netcdf(self, file_path: str):
-        """NetCDF export needs xarray + a netCDF backend (results.py:252-269); without them the arrays
-        are written to an .npz with the same variable names."""
+        """NetCDF export with the reference's layout (results.py:252-269): every data variable under its name and
+        dimensions, complex variables split into ``<name>_real`` / ``<name>_imag``, coordinates as coordinate variables.
+        With xarray + h5netcdf installed this is the reference's own call; without them (this image) the same content is
+        written as a NetCDF-3 (64-bit offset) file by ``scipy.io.netcdf_file``, which xarray / netCDF4 read back with the
+        same variable names."""
         if _xr is not None:
             ds = self.dataset
             out = {}
@@ -135,5 +138,35 @@ class Results:
                 else:
                     out[name] = (ds[name].dims, data)
             _xr.Dataset(out, coords=ds.coords).to_netcdf(file_path, engine="h5netcdf")
-        else:
-            np.savez(file_path, **{k: v.values for k, v in self.dataset.data_vars.items()})
+            return
+        from scipy.io import netcdf_file
+        ds = self.dataset
+        variables = {}
+        for name, var in ds.data_vars.items():
+            data = np.asarray(var.values)
+            if np.iscomplexobj(data):
+                variables[name + "_real"] = (var.dims, np.real(data))
+                variables[name + "_imag"] = (var.dims, np.imag(data))
+            else:
+                variables[name] = (var.dims, data)
+        sizes = {}
+        for dims, data in variables.values():
+            for d, n in zip(dims, data.shape):
+                if sizes.setdefault(d, n) != n:
+                    raise ValueError(f"dimension {d!r} has inconsistent lengths {sizes[d]} and {n}")
+        with netcdf_file(file_path, "w", version=2) as nc:
+            for d, n in sizes.items():
+                nc.createDimension(d, int(n))
+            for d in sizes:                                   # coordinate variables (numeric coordinates only)
+                c = ds.coords.get(d)
+                if c is None:
+                    continue
+                c = np.asarray(c)
+                if c.shape == (sizes[d],) and c.dtype.kind in "iuf":
+                    c = c.astype(np.float64 if c.dtype.kind == "f" else np.int32)
+                    nc.createVariable(d, c.dtype, (d,))[:] = c
+            for name, (dims, data) in variables.items():
+                data = np.ascontiguousarray(data, dtype=np.float64 if data.dtype.kind == "f" else np.int32)
+                v = nc.createVariable(name, data.dtype, tuple(dims))
+                v[:] = data
+            nc.history = "openflash_b200 Results.export_to_netcdf (NetCDF-3 fallback: xarray not installed)"

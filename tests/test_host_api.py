@@ -151,3 +151,36 @@ def test_packed_triangle_and_syrk_tile_layouts():
         assert np.array_equal(cover, np.tril(np.ones((nb, nb), int)))      # every lower block exactly once, nothing above
         assert sizes == sorted(sizes, reverse=True)                        # largest first: balanced passes of 8 warps
     assert lib.meemb200_debug_layout(1, 1000, buf, len(buf)) != 0          # too wide for the staged SYRK: refused, not garbage
+
+
+def test_results_netcdf_export_roundtrip(tmp_path):
+    """Results.export_to_netcdf (results.py:252-269): variable names, dimensions and the real / imag split survive a round
+    trip through the NetCDF file (scipy reader; xarray-free image)."""
+    from scipy.io import netcdf_file
+    geo = _geo(NMK=[3, 4, 5])
+    prob = ofb.MEEMProblem(geo)
+    om = np.array([0.5, 1.0, 2.0])
+    prob.set_frequencies(om)
+    res = ofb.Results(prob)
+    R = len(res.modes)
+    rng = np.random.default_rng(0)
+    am, dp = rng.normal(size=(3, R, R)), rng.normal(size=(3, R, R))
+    fo, ph = rng.normal(size=(3, R)), rng.normal(size=(3, R))
+    res.store_hydrodynamic_coefficients(om, am, dp, fo, ph)
+    X = rng.normal(size=(3, R, 3 + 2 * 4 + 5)) + 1j * rng.normal(size=(3, R, 3 + 2 * 4 + 5))
+    res.store_potential_coefficients(X, [3, 4, 5])
+    path = str(tmp_path / "out.nc")
+    res.export_to_netcdf(path)
+    if ofb.results._xr is not None:
+        pytest.skip("xarray present: the reference's own h5netcdf writer was used")
+    with netcdf_file(path, "r", mmap=False) as nc:
+        assert nc.variables["added_mass"].dimensions == ("frequency", "mode_i", "mode_j")
+        assert np.array_equal(nc.variables["added_mass"][:], am) and np.array_equal(nc.variables["damping"][:], dp)
+        assert nc.variables["excitation_phase"].dimensions == ("frequency", "mode_i")
+        assert np.array_equal(nc.variables["excitation_force"][:], fo)
+        assert np.array_equal(nc.variables["frequency"][:], om)
+        pr, pi = nc.variables["potentials_real"][:], nc.variables["potentials_imag"][:]
+        assert nc.variables["potentials_real"].dimensions == ("frequency", "modes", "domain_name", "harmonics")
+        assert pr.shape == (3, R, 3, 8)
+        assert np.array_equal(pr[:, :, 1, :8], X.real[:, :, 3:11]) and np.array_equal(pi[:, :, 2, :5], X.imag[:, :, 11:16])
+        assert np.isnan(pr[:, :, 0, 3:]).all()                # NaN padding to the widest domain, as in the reference
