@@ -230,8 +230,9 @@ __device__ __forceinline__ double warp_sum(double v) {
 
 // ------------------------------------------------------------------------------------------------
 // Schur path, geometry stage
-template <int NB>
-__global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int n_slots_unused) {
+template <int NB, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_geom(const void* blob, void* ws, int n_slots_unused) {
+    constexpr bool SMALL = MINB > 1;
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ int sh_item, sh_status;
@@ -258,8 +259,8 @@ __global__ void __launch_bounds__(512, 1) k_geom(const void* blob, void* ws, int
         for (int n = tid; n < N; n += nthr) W[(long)(L.pot_row[M - 1] + n) * ld + p + n] = 1.0;   // E
         for (int i = 0; i < R; ++i) fill_b_static<double>(g, L, flags + (int64_t)i * (M + 1), W + p + N + i, ld, tid, nthr);
         __syncthreads();
-        lu_forward<double, NB>(W, ld, p, p, ncols, smem, &sh_status);
-        lu_backward<double, NB>(W, ld, p, p, ncols, smem, p);
+        lu_forward<double, NB, SMALL>(W, ld, p, p, ncols, smem, &sh_status);
+        lu_backward<double, NB, SMALL>(W, ld, p, p, ncols, smem, p);
         __syncthreads();
         // reduce to what the frequency stage needs
         double* gs = v.gstore + gd.gs_off;
@@ -1953,7 +1954,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     // 256-thread CTAs, several per SM (register-limited), large ones 512 threads
     P->geom_threads = max_p <= 320 ? 256 : 512;
     if (const char* ev = getenv("MEEMB200_GEOM_THREADS")) { const int t = atoi(ev); if (t == 128 || t == 256 || t == 512) P->geom_threads = t; }
-    P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, (int64_t)sms * (512 / P->geom_threads));
+    P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, (int64_t)sms * (P->geom_threads == 512 ? 1 : 1024 / P->geom_threads));
     if (schur) {
         const int per_sm = (std::max(P->smem_freq + 24 * 1024, kGemmSmemBytes + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
@@ -2062,9 +2063,10 @@ static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, 
 }
 template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
     if (P->use_coop) return launch_geom_coop(P, in, ws, s);
-    cudaError_t e = cudaFuncSetAttribute(k_geom<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
+    auto kfn = P->geom_threads == 512 ? k_geom<NB, 512, 1> : P->geom_threads == 256 ? k_geom<NB, 256, 4> : k_geom<NB, 128, 8>;
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
     if (e != cudaSuccess) return e;
-    k_geom<NB><<<P->n_slots_geom, P->geom_threads, P->smem_geom, s>>>(in, ws, 0);
+    kfn<<<P->n_slots_geom, P->geom_threads, P->smem_geom, s>>>(in, ws, 0);
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* in, void* ws, OutPtrs o, cudaStream_t s) {

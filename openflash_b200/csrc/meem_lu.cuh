@@ -18,9 +18,12 @@ namespace meem {
 
 constexpr int kLuChunk = 512;   // columns of U12 staged per pass
 
-template <class T> struct LuTile;            // register tile of the rank-NB update
-template <> struct LuTile<double> { static constexpr int TR = 8, TC = 4; };
-template <> struct LuTile<cplx>   { static constexpr int TR = 4, TC = 2; };
+template <class T, bool SMALL = false> struct LuTile;            // register tile of the rank-NB update
+template <> struct LuTile<double, false> { static constexpr int TR = 8, TC = 4; };
+template <> struct LuTile<cplx, false>   { static constexpr int TR = 4, TC = 2; };
+// SMALL: half the accumulators, for the many-small-geometries kernel that trades tile efficiency for resident warps
+template <> struct LuTile<double, true>  { static constexpr int TR = 4, TC = 2; };
+template <> struct LuTile<cplx, true>    { static constexpr int TR = 4, TC = 2; };
 
 MEEM_HD double zero_of(double) { return 0.0; }
 MEEM_HD cplx zero_of(cplx) { return cmake(0.0, 0.0); }
@@ -40,10 +43,10 @@ __host__ __device__ constexpr size_t lu_smem_bytes(int max_rows) {
 #ifdef __CUDACC__
 
 // W[i][c] -= sum_q Lp[q*lstride + (i - row0)] * Us[q*kLuChunk + (c - c0)]  for i in [r_begin, r_end), c in [c0, c1)
-template <class T, int NB>
+template <class T, int NB, bool SMALL = false>
 __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, const T* Lp, int lstride,
                                int c0, int c1, const T* Us, int nbj) {
-    constexpr int TR = LuTile<T>::TR, TC = LuTile<T>::TC;
+    constexpr int TR = LuTile<T, SMALL>::TR, TC = LuTile<T, SMALL>::TC;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
     const int nrt = (r_end - r_begin + TR - 1) / TR;
     const int nct = (c1 - c0 + 32 * TC - 1) / (32 * TC);
@@ -90,7 +93,7 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
 // U and the transformed right-hand sides; rows >= npiv hold the Schur remainder in columns >= npiv.
 // status: bit 0 set on an exactly-zero pivot, bit 1 on a non-finite pivot column.
 // smem: lu_smem_bytes<T,NB>(nrows).  All threads of the CTA must call.
-template <class T, int NB>
+template <class T, int NB, bool SMALL = false>
 __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsigned char* smem_raw, int* status) {
     T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][nrows] column-major
     T* ust = panel + (size_t)NB * nrows;                     // [NB][kLuChunk]
@@ -180,7 +183,7 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
                 }
             }
             __syncthreads();
-            lu_rank_update<T, NB>(W, ld, k0 + nbj, nrows, k0, panel, nrows, cc0, cc1, ust, nbj);
+            lu_rank_update<T, NB, SMALL>(W, ld, k0 + nbj, nrows, k0, panel, nrows, cc0, cc1, ust, nbj);
             __syncthreads();
         }
     }
@@ -188,7 +191,7 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
 
 // Back-substitution U X = Y for right-hand-side columns [c0, c1) after lu_forward (U = rows/cols
 // [0, npiv)); X overwrites Y.  Blocked bottom-up, reusing the rank-NB update for the rows above.
-template <class T, int NB>
+template <class T, int NB, bool SMALL = false>
 __device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned char* smem_raw, int max_rows) {
     T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][max_rows]: U[0:k0+nbj, k0:k0+nbj]
     T* ust = panel + (size_t)NB * max_rows;
@@ -222,7 +225,7 @@ __device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned ch
                 }
             }
             __syncthreads();
-            lu_rank_update<T, NB>(W, ld, 0, k0, 0, panel, max_rows, cc0, cc1, ust, nbj);
+            lu_rank_update<T, NB, SMALL>(W, ld, 0, k0, 0, panel, max_rows, cc0, cc1, ust, nbj);
             __syncthreads();
         }
     }
