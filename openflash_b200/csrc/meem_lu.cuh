@@ -54,11 +54,15 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
         const int rt = t / nct, ct = t - rt * nct;
         const int i0 = r_begin + rt * TR;
         const int cb = c0 + ct * 32 * TC + lane;
+        // the accumulators start from the old entries of W: their (L2-latency) loads are in flight during the products
         T acc[TR][TC];
 #pragma unroll
         for (int r = 0; r < TR; ++r)
 #pragma unroll
-            for (int c = 0; c < TC; ++c) acc[r][c] = zero_of(T());
+            for (int c = 0; c < TC; ++c) {
+                const int cc = cb + 32 * c;
+                acc[r][c] = (i0 + r < r_end && cc < c1) ? W[(long)(i0 + r) * ld + cc] : zero_of(T());
+            }
         for (int q = 0; q < nbj; ++q) {
             T l[TR], u[TC];
 #pragma unroll
@@ -79,10 +83,7 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
 #pragma unroll
             for (int c = 0; c < TC; ++c) {
                 const int cc = cb + 32 * c;
-                if (cc < c1) {
-                    T* p = &W[(long)(i0 + r) * ld + cc];
-                    *p = *p + acc[r][c];
-                }
+                if (cc < c1) W[(long)(i0 + r) * ld + cc] = acc[r][c];
             }
         }
     }
