@@ -63,19 +63,33 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
                 const int cc = cb + 32 * c;
                 acc[r][c] = (i0 + r < r_end && cc < c1) ? W[(long)(i0 + r) * ld + cc] : zero_of(T());
             }
-        for (int q = 0; q < nbj; ++q) {
+        // rows / columns past the end re-read the last valid one (their accumulators are never stored), so the
+        // operand loads of the product loop are unconditional and address a running pointer
+        int ro[TR], co[TC];
+#pragma unroll
+        for (int r = 0; r < TR; ++r) ro[r] = min(r, r_end - 1 - i0);
+#pragma unroll
+        for (int c = 0; c < TC; ++c) co[c] = min(cb + 32 * c, c1 - 1) - cb;
+        const T* lp = Lp + (i0 - row0);
+        const T* up = Us + (cb - c0);
+        auto step = [&]() {
             T l[TR], u[TC];
 #pragma unroll
-            for (int r = 0; r < TR; ++r) l[r] = (i0 + r < r_end) ? Lp[q * lstride + (i0 + r - row0)] : zero_of(T());
+            for (int r = 0; r < TR; ++r) l[r] = lp[ro[r]];
 #pragma unroll
-            for (int c = 0; c < TC; ++c) {
-                const int cc = cb + 32 * c;
-                u[c] = (cc < c1) ? Us[q * kLuChunk + (cc - c0)] : zero_of(T());
-            }
+            for (int c = 0; c < TC; ++c) u[c] = up[co[c]];
 #pragma unroll
             for (int r = 0; r < TR; ++r)
 #pragma unroll
                 for (int c = 0; c < TC; ++c) fnma(acc[r][c], l[r], u[c]);
+            lp += lstride;
+            up += kLuChunk;
+        };
+        if (nbj == NB) {
+#pragma unroll
+            for (int q = 0; q < NB; ++q) step();
+        } else {
+            for (int q = 0; q < nbj; ++q) step();
         }
 #pragma unroll
         for (int r = 0; r < TR; ++r) {
