@@ -47,7 +47,10 @@ def main():
             base = h.split(".TriageCompute.")[-1] if ".TriageCompute." in h else h
             if base in KEEP and r[i] != "":
                 out.append(f"{base} [{units[i]}] = {r[i]}")
-                vals[base] = (float(r[i].replace(",", "")), units[i])
+                try:
+                    vals[base] = (float(r[i].replace(",", "")), units[i])
+                except ValueError:                              # "no data" for a metric ncu could not collect
+                    pass
         def to_bytes(key):
             v, u = vals.get(key, (0.0, "byte"))
             return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
