@@ -626,7 +626,8 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ Exterior ex;
-    __shared__ int sh_item, sh_status, sh_scan;
+    __shared__ int sh_item, sh_status;
+    __shared__ int64_t sh_scan;
     __shared__ GemmSmem gsm;
     DevView v = make_view(blob, ws);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -638,19 +639,26 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
     __syncthreads();
     for (;;) {
         int item;
-        if (only_flagged) {      // static striding: every CTA scans its share of the status words
-            if (tid == 0) {
-                int it = sh_scan;
-                for (; it < total; it += gridDim.x) {
+        if (only_flagged) {      // static striding: every CTA scans its share of the status words, blockDim.x of them at a time
+            for (;;) {
+                const int64_t base = sh_scan;
+                const int64_t it = base + (int64_t)tid * gridDim.x;
+                bool flagged = false;
+                if (it < total) {
                     const int gi_ = v.order[it / F];
-                    if (out.status[v.geom[gi_].out_sys + it % F] & 4) break;
+                    flagged = (out.status[v.geom[gi_].out_sys + it % F] & 4) != 0;
                 }
-                sh_item = it;
-                sh_scan = it + gridDim.x;
+                if (tid == 0) sh_item = 0x7fffffff;
+                __syncthreads();
+                if (flagged) atomicMin(&sh_item, (int)it);
+                __syncthreads();
+                item = sh_item;
+                const int64_t next = (item != 0x7fffffff) ? (int64_t)item + gridDim.x : base + (int64_t)nthr * gridDim.x;
+                __syncthreads();
+                if (tid == 0) sh_scan = next;
+                __syncthreads();
+                if (item != 0x7fffffff || next >= total) break;
             }
-            __syncthreads();
-            item = sh_item;
-            __syncthreads();
         } else {
             item = next_item(&v.counters[2], &sh_item);
         }
@@ -1136,9 +1144,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
             if (lane == 0 && t < 64) sh_dots[t] = a;
         }
         __syncthreads();
-        const int fail = sh_fail;
-        const int status = gstatus | (fail ? 4 : 0);
         const int64_t sysi = gd.out_sys + f;
+        const int flag_every = flags >> 8;                          // test hook: send every n-th system down the LU re-solve
+        const int fail = sh_fail | (flag_every > 0 && sysi % flag_every == 0);
+        const int status = gstatus | (fail ? 4 : 0);
         if (tid == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
         const double ze = linv_last * linv_last;
         const double den = 1.0 + beta * beta * ze * ze;
@@ -1263,7 +1272,8 @@ struct SmallWs {
     int fail;
 };
 
-__global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* blob, void* ws, OutPtrs out, int n_items, int* counter) {
+__global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* blob, void* ws, OutPtrs out, int n_items, int* counter,
+                                                                   int flag_every) {
     extern __shared__ __align__(16) unsigned char smem[];
     DevView v = make_view(blob, ws);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1416,8 +1426,8 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         }
         __syncwarp();
         // 6. coefficients (same closure as k_freq_solve)
-        const int status = gstatus | (S.fail ? 4 : 0);
         const int64_t sysi = gd.out_sys + f;
+        const int status = gstatus | ((S.fail || (flag_every > 0 && sysi % flag_every == 0)) ? 4 : 0);
         if (lane == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
         const double linv_last = S.Li[(K - 1) * kCholLdP + K - 1];
         const double beta = S.beta;
@@ -1920,6 +1930,10 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0);
+    if (const char* ev = getenv("MEEMB200_TEST_FLAG_EVERY")) {     // tests: every n-th system is treated as a failed Cholesky
+        const int n = atoi(ev);
+        if (n > 0 && n < (1 << 20)) P->gemm_flags |= n << 8;
+    }
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
@@ -2087,7 +2101,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
         int* wave_counters = reinterpret_cast<int*>(static_cast<char*>(ws) + h->ws_counters + 256);
         const int64_t n_sys = P->info.n_sys;
         const int grid = (int)std::min<int64_t>((n_sys + kSmallWarps - 1) / kSmallWarps, P->solve_grid);
-        k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters);
+        k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters, P->gemm_flags >> 8);
         cudaEventRecord(P->ev[3], s);
         cudaEventRecord(P->ev[4], s);
         e = cudaGetLastError();

@@ -268,6 +268,41 @@ def test_schur_kernel_variants_vs_reference(ofb, monkeypatch, name, env):
     _check(res2, ref)
 
 
+@pytest.mark.parametrize("small", [False, True], ids=["k_freq_solve", "k_freq_small"])
+def test_failed_cholesky_systems_are_resolved_by_lu(ofb, monkeypatch, small):
+    """A system whose Cholesky reports a non-positive pivot (status bit 2) is re-solved by the pivoted LU of the unreduced
+    K x K system (k_freq_lu, only_flagged pass) and leaves with status 0.  MEEMB200_TEST_FLAG_EVERY=3 makes the solve kernels
+    report every third system as failed: those systems must come back within the parity bar (and not bit-identical to the
+    Cholesky answer - the re-solve really ran), the others bit-identical to the unhooked run.  The scan for flagged systems
+    covers more systems than one CTA pass (blockDim x gridDim), so its chunked loop wraps."""
+    if small:
+        h, a, d, NMK, bm, modes = 1.001, [0.125, 0.25], [0.25, 0.125], [10, 10, 10], [0, 0], [0]
+        om = np.linspace(0.1, 3.0, 600)
+    else:
+        h, a, d, NMK, bm, modes = 20.0, [5.0, 10.0, 15.0], [15.0, 10.0, 5.0], [20, 20, 20, 20], [0, 1, 2], [0, 1, 2]
+        om = np.linspace(0.2, 3.0, 60)
+    geo = ofb.FlatGeometry.from_body_map(h, a, d, NMK, bm, modes)
+    # many copies of the geometry: > 296 CTAs x 256 threads status words for the k_freq_solve case would be slow, so the
+    # wrap-around of the scan is exercised with the small systems (600 omega x 160 geometries = 96 000 systems)
+    geos = [geo] * (160 if small else 2)
+    plain = ofb.solve_batch(geos, om)
+    monkeypatch.setenv("MEEMB200_TEST_FLAG_EVERY", "3")
+    hooked = ofb.solve_batch(geos, om)
+    ref = mo.run_sweep(mo.FlatGeometry(h, a, d, NMK), om, bm, modes)
+    F = len(om)
+    differs = 0
+    for gi, (rp, rh) in enumerate(zip(plain, hooked)):
+        assert np.all(rh["status"] == 0) and np.all(rp["status"] == 0)
+        if gi < 2 or gi == len(geos) - 1:
+            _check(rh, ref)
+        flagged = (gi * F + np.arange(F)) % 3 == 0
+        for v in ("added_mass", "damping", "excitation_force"):
+            assert np.array_equal(rp[v][~flagged], rh[v][~flagged])
+            differs += int(np.any(rp[v][flagged] != rh[v][flagged]))
+            np.testing.assert_allclose(rh[v][flagged], rp[v][flagged], rtol=1e-8, atol=1e-10 * np.max(np.abs(rp[v])))
+    assert differs > 0
+
+
 @pytest.mark.parametrize("geom", ["small_bicylinder", "small_tricylinder"])
 def test_mode_count_convergence_sweep_c5(ofb, geom):
     """BASELINE.json configs[4]: mode-count convergence sweep, equal modes per region, outputs incl. the excitation
