@@ -234,64 +234,71 @@ MEEM_HD void fill_tables(const Geom& g, const Layout& L, double* tab, int tid, i
 // omega-independent blocks (eng.py:164-276 minus the closures registered at :177-188, :229-246).
 // Only entries with row < rlim and col < rlim are written (rlim = p for the Schur path's A11,
 // N_T for the dense matrix).  The target must be zeroed beforehand.
+// Rows of ONE boundary: potential rows at row rp, velocity rows at row rv, columns shifted by -cshift (the window
+// elimination of k_geom_band places boundary bd's rows into a window whose column 0 is region bd's first column;
+// the full matrix uses rp = L.pot_row[bd], rv = L.vel_row[bd], cshift = 0).  The last boundary writes only its
+// omega-independent potential-row diagonal blocks.
 template <class T>
-MEEM_HD void fill_A_static(const Geom& g, const Layout& L, const double* tab, T* A, long ld, int tid, int nthr) {
+MEEM_HD void fill_A_boundary(const Geom& g, const Layout& L, const double* tab, int bd, T* A, long ld, int rp, int rv,
+                             int cshift, int tid, int nthr) {
     const int M = g.M;
-    for (int bd = 0; bd < M; ++bd) {
-        const int N = g.nmk[bd];
-        const double* TL = tab + L.tab[bd];
-        const int c1L = L.col[bd], c2L = c1L + N;
-        const double hdL = g.h - g.d[bd];
-        const int rp = L.pot_row[bd], rv = L.vel_row[bd];
-        if (bd == M - 1) {
-            for (int n = tid; n < N; n += nthr) {
-                set_real(A[(long)(rp + n) * ld + c1L + n], hdL * TL[0 * N + n]);
-                if (bd > 0) set_real(A[(long)(rp + n) * ld + c2L + n], hdL * TL[1 * N + n]);
-            }
-            continue;
+    const int N = g.nmk[bd];
+    const double* TL = tab + L.tab[bd];
+    const int c1L = L.col[bd] - cshift, c2L = c1L + N;
+    const double hdL = g.h - g.d[bd];
+    if (bd == M - 1) {
+        for (int n = tid; n < N; n += nthr) {
+            set_real(A[(long)(rp + n) * ld + c1L + n], hdL * TL[0 * N + n]);
+            if (bd > 0) set_real(A[(long)(rp + n) * ld + c2L + n], hdL * TL[1 * N + n]);
         }
-        const int Mm = g.nmk[bd + 1];
-        const double* TR = tab + L.tab[bd + 1];
-        const int cR = L.col[bd + 1];
-        const double hdR = g.h - g.d[bd + 1];
-        const bool pot_left_diag = g.d[bd] > g.d[bd + 1];
-        // diagonal blocks
-        if (pot_left_diag) {
-            for (int n = tid; n < N; n += nthr) {
-                set_real(A[(long)(rp + n) * ld + c1L + n], hdL * TL[0 * N + n]);
-                if (bd > 0) set_real(A[(long)(rp + n) * ld + c2L + n], hdL * TL[1 * N + n]);
-            }
-            for (int m = tid; m < Mm; m += nthr) {       // velocity rows use region bd+1's modes
-                set_real(A[(long)(rv + m) * ld + cR + m], hdR * TR[6 * Mm + m]);
-                set_real(A[(long)(rv + m) * ld + cR + Mm + m], hdR * TR[7 * Mm + m]);
-            }
-        } else {
-            for (int m = tid; m < Mm; m += nthr) {
-                set_real(A[(long)(rp + m) * ld + cR + m], -(hdR * TR[4 * Mm + m]));
-                set_real(A[(long)(rp + m) * ld + cR + Mm + m], -(hdR * TR[5 * Mm + m]));
-            }
-            for (int n = tid; n < N; n += nthr) {
-                set_real(A[(long)(rv + n) * ld + c1L + n], -(hdL * TL[2 * N + n]));
-                if (bd > 0) set_real(A[(long)(rv + n) * ld + c2L + n], -(hdL * TL[3 * N + n]));
-            }
+        return;
+    }
+    const int Mm = g.nmk[bd + 1];
+    const double* TR = tab + L.tab[bd + 1];
+    const int cR = L.col[bd + 1] - cshift;
+    const double hdR = g.h - g.d[bd + 1];
+    const bool pot_left_diag = g.d[bd] > g.d[bd + 1];
+    // diagonal blocks
+    if (pot_left_diag) {
+        for (int n = tid; n < N; n += nthr) {
+            set_real(A[(long)(rp + n) * ld + c1L + n], hdL * TL[0 * N + n]);
+            if (bd > 0) set_real(A[(long)(rp + n) * ld + c2L + n], hdL * TL[1 * N + n]);
         }
-        // dense blocks
-        for (int e = tid; e < N * Mm; e += nthr) {
-            const int n = e / Mm, m = e - n * Mm;
-            const double I = inm(n, m, bd, g);
-            if (pot_left_diag) {
-                set_real(A[(long)(rp + n) * ld + cR + m], -(TR[4 * Mm + m] * I));
-                set_real(A[(long)(rp + n) * ld + cR + Mm + m], -(TR[5 * Mm + m] * I));
-                set_real(A[(long)(rv + m) * ld + c1L + n], -(TL[2 * N + n] * I));
-                if (bd > 0) set_real(A[(long)(rv + m) * ld + c2L + n], -(TL[3 * N + n] * I));
-            } else {
-                set_real(A[(long)(rp + m) * ld + c1L + n], TL[0 * N + n] * I);
-                if (bd > 0) set_real(A[(long)(rp + m) * ld + c2L + n], TL[1 * N + n] * I);
-                set_real(A[(long)(rv + n) * ld + cR + m], TR[6 * Mm + m] * I);
-                set_real(A[(long)(rv + n) * ld + cR + Mm + m], TR[7 * Mm + m] * I);
-            }
+        for (int m = tid; m < Mm; m += nthr) {       // velocity rows use region bd+1's modes
+            set_real(A[(long)(rv + m) * ld + cR + m], hdR * TR[6 * Mm + m]);
+            set_real(A[(long)(rv + m) * ld + cR + Mm + m], hdR * TR[7 * Mm + m]);
+        }
+    } else {
+        for (int m = tid; m < Mm; m += nthr) {
+            set_real(A[(long)(rp + m) * ld + cR + m], -(hdR * TR[4 * Mm + m]));
+            set_real(A[(long)(rp + m) * ld + cR + Mm + m], -(hdR * TR[5 * Mm + m]));
+        }
+        for (int n = tid; n < N; n += nthr) {
+            set_real(A[(long)(rv + n) * ld + c1L + n], -(hdL * TL[2 * N + n]));
+            if (bd > 0) set_real(A[(long)(rv + n) * ld + c2L + n], -(hdL * TL[3 * N + n]));
         }
     }
+    // dense blocks
+    for (int e = tid; e < N * Mm; e += nthr) {
+        const int n = e / Mm, m = e - n * Mm;
+        const double I = inm(n, m, bd, g);
+        if (pot_left_diag) {
+            set_real(A[(long)(rp + n) * ld + cR + m], -(TR[4 * Mm + m] * I));
+            set_real(A[(long)(rp + n) * ld + cR + Mm + m], -(TR[5 * Mm + m] * I));
+            set_real(A[(long)(rv + m) * ld + c1L + n], -(TL[2 * N + n] * I));
+            if (bd > 0) set_real(A[(long)(rv + m) * ld + c2L + n], -(TL[3 * N + n] * I));
+        } else {
+            set_real(A[(long)(rp + m) * ld + c1L + n], TL[0 * N + n] * I);
+            if (bd > 0) set_real(A[(long)(rp + m) * ld + c2L + n], TL[1 * N + n] * I);
+            set_real(A[(long)(rv + n) * ld + cR + m], TR[6 * Mm + m] * I);
+            set_real(A[(long)(rv + n) * ld + cR + Mm + m], TR[7 * Mm + m] * I);
+        }
+    }
+}
+
+template <class T>
+MEEM_HD void fill_A_static(const Geom& g, const Layout& L, const double* tab, T* A, long ld, int tid, int nthr) {
+    for (int bd = 0; bd < g.M; ++bd) fill_A_boundary<T>(g, L, tab, bd, A, ld, L.pot_row[bd], L.vel_row[bd], 0, tid, nthr);
 }
 
 // omega-dependent blocks of the last boundary (eng.py:177-188, :229-246; me.py:529-536, :563-576).

@@ -18,6 +18,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
 #include <cstdlib>
 #include <cmath>
 #include <string>
@@ -28,6 +29,7 @@
 #include "meem_lu.cuh"
 #include "meem_chol.cuh"
 #include "meem_geom_coop.cuh"
+#include "meem_geom_band.cuh"
 
 using namespace meem;
 
@@ -42,7 +44,7 @@ struct GeomDesc {
     int64_t tab_off;             // doubles, into tables workspace
     int64_t gs_off;              // doubles, into geometry-stage store
     int64_t xg_off;              // doubles, into (G, y0) store (want_x) or -1
-    int64_t out_rr, out_r, out_sys, out_x;
+    int64_t out_rr, out_r, out_sys, out_x, out_c;
     double h;
 };
 struct RootSet {
@@ -139,6 +141,19 @@ struct OutPtrs {
     double* x;
 };
 
+// c vectors (meem_engine.py:65-98) of every radiating mode of every geometry: out[g][j][p_g], frequency independent.
+__global__ void k_cvec(const void* blob, void* ws, double* out) {
+    DevView v = make_view(blob, ws);
+    __shared__ Layout L;
+    const GeomDesc gd = v.geom[blockIdx.x];
+    const Geom g = geom_of(v, gd);
+    if (threadIdx.x == 0) make_layout(g, L);
+    __syncthreads();
+    for (int j = 0; j < gd.R; ++j)
+        fill_c<double>(g, L, v.tables + gd.tab_off, v.flags + gd.flag_off + (int64_t)j * (gd.M + 1),
+                       out + gd.out_c + (int64_t)j * gd.p, threadIdx.x, blockDim.x);
+}
+
 // ------------------------------------------------------------------------------------------------
 // roots
 __global__ void k_m0(const void* blob, void* ws) {
@@ -156,17 +171,18 @@ __global__ void k_m0(const void* blob, void* ws) {
 __global__ void k_mk(const void* blob, void* ws) {
     DevView v = make_view(blob, ws);
     const int F = v.hdr->n_freq;
-    const int s = blockIdx.y;
-    const RootSet rs = v.sets[s];
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= F * rs.K) return;
-    const int f = t / rs.K, k = t - f * rs.K;
-    const double m0 = v.roots[rs.off + f];
-    const double mk = mk_entry(k, m0, rs.h, v.hdr->root_mode);
-    double* mkp = v.roots + rs.off + F;
-    double* nkp = mkp + (int64_t)F * rs.K;
-    mkp[(int64_t)f * rs.K + k] = mk;
-    nkp[(int64_t)f * rs.K + k] = nk_entry(k, m0, rs.h, mk);
+    for (int s = blockIdx.y; s < v.hdr->n_sets; s += gridDim.y) {      // gridDim.y is capped at 65 535 root sets per pass
+        const RootSet rs = v.sets[s];
+        if (t >= F * rs.K) continue;
+        const int f = t / rs.K, k = t - f * rs.K;
+        const double m0 = v.roots[rs.off + f];
+        const double mk = mk_entry(k, m0, rs.h, v.hdr->root_mode);
+        double* mkp = v.roots + rs.off + F;
+        double* nkp = mkp + (int64_t)F * rs.K;
+        mkp[(int64_t)f * rs.K + k] = mk;
+        nkp[(int64_t)f * rs.K + k] = nk_entry(k, m0, rs.h, mk);
+    }
 }
 
 __global__ void k_roots_flat(int n, int K, const double* freq, const double* h, int freq_kind, int root_mode,
@@ -327,6 +343,81 @@ __global__ void __launch_bounds__(THREADS, MINB) k_geom(const void* blob, void* 
                 const int r = (int)(e / (N + R)), c = (int)(e - (int64_t)r * (N + R));
                 xg[e] = W[(long)r * ld + p + c];
             }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, geometry stage by window elimination (meem_geom_band.cuh): one CTA per geometry, the window in shared
+// memory (SMEMWIN: dynamic smem = LU scratch | window | hand-over buffer) or in the CTA's L2-resident global slot.
+// Used whenever X is not requested (the X reconstruction needs all of G, which only the dense elimination forms).
+__host__ __device__ inline int band_ld(int wcols, bool smem) { return smem ? (wcols | 1) : ((wcols + 1) & ~1); }
+template <int NB, int THREADS, int MINB, bool SMALL, bool SMEMWIN, int CHUNK>
+__global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, void* ws, int wrows_max, int wcols_max) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ int sh_item, sh_status;
+    DevView v = make_view(blob, ws);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const long ld = band_ld(wcols_max, SMEMWIN);
+    const size_t lu_bytes = (lu_smem_bytes<double, NB, CHUNK>(wrows_max) + 15) & ~(size_t)15;
+    double* W = SMEMWIN ? reinterpret_cast<double*>(smem + lu_bytes) : v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_geom;
+    double* side = W + (long)wrows_max * ld;
+    for (;;) {
+        const int item = next_item(&v.counters[0], &sh_item);
+        if (item >= v.hdr->n_geom) break;
+        const int gi = v.order[item];
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        if (tid == 0) { make_layout(g, L); sh_status = 0; }
+        __syncthreads();
+        const int N = gd.N, R = gd.R, M = gd.M;
+        const double* tab = v.tables + gd.tab_off;
+        const uint8_t* flags = v.flags + gd.flag_off;
+        band_eliminate<NB, SMALL, CHUNK>(g, L, tab, flags, R, W, ld, side, smem, &sh_status);
+        // reduce to what the frequency stage needs (same store layout as k_geom)
+        double* gs = v.gstore + gd.gs_off;
+        double* HT = gs;
+        const int ldn = gs_ldn(N, R);
+        double* wv = HT + (int64_t)N * ldn;
+        double* uv = wv + (int64_t)R * N;
+        double* s0 = uv + (int64_t)R * N;
+        double* phi = s0 + R * R;
+        double* bc = phi + R;
+        double* st = bc + R;
+        const int bd = M - 1;
+        const int n0 = band_unknowns(g, bd);
+        const double* TL = tab + L.tab[bd];
+        // H[n][n'] = R1'(a)[n] G[C1 row n][n'] + R2'(a)[n] G[C2 row n][n'];  stored transposed
+        for (int e = tid; e < N * N; e += nthr) {
+            const int n2 = e / N, n = e - n2 * N;
+            double hv = TL[2 * N + n] * W[(long)n * ld + n0 + n2];
+            if (bd > 0) hv += TL[3 * N + n] * W[(long)(N + n) * ld + n0 + n2];
+            HT[(int64_t)n2 * ldn + n] = hv;
+        }
+        for (int e = tid; e < R * N; e += nthr) {
+            const int i = e / N, n = e - i * N;
+            double u = TL[2 * N + n] * W[(long)n * ld + n0 + N + i];
+            if (bd > 0) u += TL[3 * N + n] * W[(long)(N + n) * ld + n0 + N + i];
+            uv[e] = u;
+            wv[e] = -W[(long)(n0 + i) * ld + n0 + n];
+        }
+        for (int e = tid; e < R * R; e += nthr) {
+            const int j = e / R, i = e - j * R;
+            s0[e] = -W[(long)(n0 + j) * ld + n0 + N + i];
+        }
+        for (int j = tid; j < R; j += nthr) {
+            phi[j] = phi_sum(g, L, tab, flags + (int64_t)j * (M + 1));
+            bc[j] = b_end_constant(g, flags + (int64_t)j * (M + 1));
+        }
+        if (tid == 0) st[0] = (double)sh_status;
+        __syncthreads();
+        for (int e = tid; e < N * (ldn - N); e += nthr) {
+            const int n = e / (ldn - N), c = e - n * (ldn - N);
+            double val = 0.0;
+            if (c < R) val = uv[c * N + n] + (n == 0 ? bc[c] : 0.0);
+            else if (c < 2 * R) val = wv[(c - R) * N + n];
+            HT[(int64_t)n * ldn + N + c] = val;
         }
     }
 }
@@ -1758,6 +1849,15 @@ struct meemb200_ctx {
     int sm_count;
     size_t smem_optin;
 };
+// Launches go to the context's device whatever the caller's current device is; the caller's choice is restored.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
 
 struct meemb200_plan {
     meemb200_ctx* ctx;
@@ -1775,6 +1875,10 @@ struct meemb200_plan {
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
     int algo;
     bool use_coop;          // grid-cooperative geometry stage (few large geometries)
+    int band_variant;       // geometry stage by window elimination (k_geom_band): -1 off, 0 small window in shared memory (128 threads),
+                            // 1 window in shared memory (256 threads), 2 window in the CTA's global slot (512 threads)
+    int band_wrows, band_wcols, band_grid;
+    size_t smem_band;
     int64_t wave_items;     // systems per frequency-stage wave
     int n_waves, solve_grid;
     int solve_variant;      // k_freq_solve: 0 = P in its L2-resident buffer (128 threads), 1/2/3 = P resident in shared memory, 128/256/512 threads
@@ -1784,7 +1888,7 @@ struct meemb200_plan {
     bool ev_ok;
 };
 
-extern "C" int meemb200_version(void) { return 100; }
+extern "C" int meemb200_version(void) { return 200; }
 extern "C" const char* meemb200_last_error(void) { return g_err.c_str(); }
 
 extern "C" int meemb200_create(int device, meemb200_ctx** out) {
@@ -1796,7 +1900,6 @@ extern "C" int meemb200_create(int device, meemb200_ctx** out) {
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) return fail(MEEMB200_ENODEV, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + ", this library is built for sm_100a only");
-    CUDA_TRY(cudaSetDevice(device));
     meemb200_ctx* c = new meemb200_ctx;
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
@@ -1831,6 +1934,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     if (b->root_mode != MEEMB200_ROOTS_REFERENCE && b->root_mode != MEEMB200_ROOTS_CONVERGED) return fail(MEEMB200_EINVAL, "unknown root_mode");
     if (b->freq_kind != MEEMB200_FREQ_OMEGA && b->freq_kind != MEEMB200_FREQ_M0) return fail(MEEMB200_EINVAL, "unknown freq_kind");
     const int G = b->n_geom, F = b->n_freq;
+    if ((int64_t)G * F > 0x7fffffffLL) return fail(MEEMB200_EINVAL, "n_geom * n_freq must fit 31 bits (work-item indices are int32): split the batch");
     for (int f = 0; f < F; ++f) {
         const double w = b->freq[f];
         if (!(w > 0.0)) return fail(MEEMB200_EINVAL, "frequencies must be positive (meem_problem.py:31)");
@@ -1841,10 +1945,12 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->ev_ok = false;
     P->geoms.resize(G);
     std::vector<RootSet> sets;
+    std::map<std::pair<uint64_t, int>, int> set_index;
     std::vector<double> cost(G);
-    int64_t n_rr = 0, n_r = 0, n_x = 0, tab_tot = 0, gs_tot = 0, xg_tot = 0;
+    int64_t n_rr = 0, n_r = 0, n_x = 0, n_c = 0, tab_tot = 0, gs_tot = 0, xg_tot = 0;
     int64_t slot_geom = 0, slot_freq = 0, slot_dense = 0;
     int max_p = 1, max_K = 1, max_NT = 1, max_N = 1;
+    int band_wrows = 0, band_wcols = 0, band_side = 0;
     double flops = 0.0;
     const int64_t total_regs = b->reg_off[G];
     for (int gi = 0; gi < G; ++gi) {
@@ -1873,11 +1979,11 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         gd.M = M; gd.R = R; gd.K = L.K; gd.N = b->nmk[r0 + M - 1];
         gd.NT = L.NT; gd.p = L.p; gd.reg_off = r0; gd.h = h;
         gd.flag_off = b->flag_off[gi];
-        int s = -1;
-        for (size_t q = 0; q < sets.size(); ++q)
-            if (sets[q].h == h && sets[q].K == L.K) { s = (int)q; break; }
-        if (s < 0) { RootSet rs; rs.h = h; rs.K = L.K; rs.pad = 0; rs.off = 0; sets.push_back(rs); s = (int)sets.size() - 1; }
-        gd.root_set = s;
+        uint64_t hbits;
+        memcpy(&hbits, &h, 8);
+        auto ins = set_index.emplace(std::make_pair(hbits, L.K), (int)sets.size());       // roots depend on (h, K) only
+        if (ins.second) { RootSet rs; rs.h = h; rs.K = L.K; rs.pad = 0; rs.off = 0; sets.push_back(rs); }
+        gd.root_set = ins.first->second;
         gd.tab_off = tab_tot; tab_tot += table_doubles(L);
         gd.gs_off = gs_tot; gs_tot += gs_doubles(gd.N, R);
         if (b->want_x && schur) { gd.xg_off = xg_tot; xg_tot += (int64_t)gd.p * (gd.N + R); }
@@ -1886,7 +1992,13 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         gd.out_r = n_r; n_r += (int64_t)F * R;
         gd.out_sys = (int64_t)gi * F;
         gd.out_x = n_x; if (b->want_x) n_x += (int64_t)F * R * gd.NT;
+        gd.out_c = n_c; n_c += (int64_t)R * gd.p;
         slot_geom = std::max<int64_t>(slot_geom, (int64_t)gd.p * (gd.p + gd.N + R));
+        {
+            BandDims D;
+            band_dims(g, L, R, D);
+            band_wrows = std::max(band_wrows, D.wrows); band_wcols = std::max(band_wcols, D.wcols); band_side = std::max(band_side, D.side);
+        }
         slot_freq = std::max<int64_t>(slot_freq, std::max(freq_slot_doubles(gd.N, gd.K, R), freq2_slot_doubles(gd.N, gd.K, R)));
         slot_dense = std::max<int64_t>(slot_dense, 2LL * gd.NT * (gd.NT + R));
         max_p = std::max(max_p, gd.p); max_K = std::max(max_K, gd.K); max_NT = std::max(max_NT, gd.NT); max_N = std::max(max_N, gd.N);
@@ -1959,6 +2071,20 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         if (P->use_coop)
             for (int gi = 0; gi < G; ++gi) slot_geom = std::max<int64_t>(slot_geom, coop_slot_doubles(P->geoms[gi].p, P->geoms[gi].N, P->geoms[gi].R));
     }
+    P->band_variant = -1; P->band_wrows = band_wrows; P->band_wcols = band_wcols; P->band_grid = 0; P->smem_band = 0;
+    if (schur && !b->want_x && !P->use_coop && !getenv("MEEMB200_NO_BAND")) {
+        // window elimination instead of the dense p x p LU (meem_geom_band.cuh); X needs all of G and keeps the dense form
+        const size_t win_s = 8 * ((size_t)band_wrows * band_ld(band_wcols, true) + band_side);
+        const size_t s0 = align_up(lu_smem_bytes<double, 8, 128>(band_wrows), 16) + win_s;
+        const size_t s1 = align_up(lu_smem_bytes<double, 8, kLuChunk>(band_wrows), 16) + win_s;
+        const size_t s2 = align_up(lu_smem_bytes<double, 8, kLuChunk>(band_wrows), 16);
+        int want = -1;
+        if (const char* ev = getenv("MEEMB200_BAND_VARIANT")) want = atoi(ev);     // tuning / test override
+        if ((want < 0 || want == 0) && s0 + 2048 <= limit / 4) { P->band_variant = 0; P->smem_band = s0; }
+        else if ((want < 0 || want == 1 || want == 0) && s1 + 2048 <= limit) { P->band_variant = 1; P->smem_band = s1; }
+        else if (s2 + 2048 <= limit) { P->band_variant = 2; P->smem_band = s2; }
+        if (P->band_variant >= 0) slot_geom = P->band_variant == 2 ? (int64_t)band_wrows * band_ld(band_wcols, false) + band_side : 0;
+    }
     P->smem_geom = P->nb_geom ? nb_bytes<double>(P->nb_geom, max_p) : 0;
     P->smem_freq = P->nb_freq ? nb_bytes<double>(P->nb_freq, max_K) : 0;
     P->smem_dense = P->nb_dense ? nb_bytes<cplx>(P->nb_dense, max_NT) : 0;
@@ -1969,6 +2095,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->geom_threads = max_p <= 320 ? 256 : 512;
     if (const char* ev = getenv("MEEMB200_GEOM_THREADS")) { const int t = atoi(ev); if (t == 128 || t == 256 || t == 512) P->geom_threads = t; }
     P->n_slots_geom = P->use_coop ? 1 : (int)std::min<int64_t>(G, (int64_t)sms * (P->geom_threads == 512 ? 1 : 1024 / P->geom_threads));
+    if (P->band_variant >= 0) P->n_slots_geom = (int)std::min<int64_t>(G, sms);
     if (schur) {
         const int per_sm = (std::max(P->smem_freq + 24 * 1024, kGemmSmemBytes + 4096) <= limit / 2) ? 2 : 1;
         P->n_slots_work = (int)std::min<int64_t>(n_sys, (int64_t)sms * per_sm);
@@ -1999,6 +2126,10 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     for (int gi = 0; gi < G; ++gi) sys_stride = std::max<int64_t>(sys_stride, freq2_sys_doubles(P->geoms[gi].K, P->geoms[gi].R));
     sys_stride = (sys_stride + 7) & ~7LL;
     P->wave_items = (int64_t)std::max<int64_t>(4 * P->n_slots_work, (int64_t)(1.5e9 / (8.0 * sys_stride)));
+    if (const char* ev = getenv("MEEMB200_WAVE_ITEMS")) {          // tuning / test override: systems per frequency-stage wave
+        const long long n = atoll(ev);
+        if (n > 0) P->wave_items = n;
+    }
     P->wave_items = std::min<int64_t>(P->wave_items, n_sys);
     P->n_waves = b->algo == MEEMB200_ALGO_SCHUR ? (int)((n_sys + P->wave_items - 1) / P->wave_items) : 0;
     H.sys_stride = sys_stride;
@@ -2031,7 +2162,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     // a[M] of each geometry is documented as inf; it is never read
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
-    P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x;
+    P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x; P->info.n_c = n_c;
     P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
@@ -2050,17 +2181,20 @@ extern "C" int meemb200_plan_info(const meemb200_plan* p, MeemPlanInfo* info) {
     return MEEMB200_OK;
 }
 extern "C" const void* meemb200_plan_blob(const meemb200_plan* p) { return p ? p->blob.data() : nullptr; }
-extern "C" int meemb200_plan_offsets(const meemb200_plan* p, int32_t g, int64_t out[6]) {
+extern "C" int meemb200_plan_offsets(const meemb200_plan* p, int32_t g, int64_t out[8]) {
     if (!p || !out || g < 0 || g >= (int)p->geoms.size()) return fail(MEEMB200_EINVAL, "bad geometry index");
     const GeomDesc& gd = p->geoms[g];
     out[0] = gd.out_rr; out[1] = gd.out_r; out[2] = gd.out_sys; out[3] = gd.out_x; out[4] = gd.NT; out[5] = gd.p;
+    out[6] = gd.out_c; out[7] = gd.R;
     return MEEMB200_OK;
 }
 extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
     if (!p || !freq) return fail(MEEMB200_EINVAL, "NULL argument");
     const BlobHeader* h = p->hdr();
-    for (int f = 0; f < h->n_freq; ++f)
-        if (!(freq[f] > 0.0)) return fail(MEEMB200_EINVAL, "frequencies must be positive");
+    for (int f = 0; f < h->n_freq; ++f) {
+        if (!(freq[f] > 0.0)) return fail(MEEMB200_EINVAL, "frequencies must be positive (meem_problem.py:31)");
+        if (std::isinf(freq[f]) && h->freq_kind == MEEMB200_FREQ_OMEGA) return fail(MEEMB200_EINVAL, "omega must be finite; pass m0=inf with FREQ_M0");
+    }
     memcpy(p->blob.data() + h->off_freq, freq, 8 * (size_t)h->n_freq);
     return MEEMB200_OK;
 }
@@ -2075,8 +2209,28 @@ static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, 
     void* args[] = {(void*)&in, (void*)&ws};
     return cudaLaunchCooperativeKernel((void*)k_geom_coop, dim3(P->ctx->sm_count), dim3(kCoopThreads), args, P->smem_coop, s);
 }
+static cudaError_t launch_geom_band(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    typedef void (*band_fn)(const void*, void*, int, int);
+    static const band_fn fns[3] = {k_geom_band<8, 128, 4, true, true, 128>, k_geom_band<8, 256, 2, false, true, kLuChunk>,
+                                   k_geom_band<8, 512, 1, false, false, kLuChunk>};
+    static const int thr[3] = {128, 256, 512};
+    const band_fn kfn = fns[P->band_variant];
+    const int nthr = thr[P->band_variant];
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_band);
+    if (e != cudaSuccess) return e;
+    if (!P->band_grid) {
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, nthr, P->smem_band);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        P->band_grid = P->band_variant == 2 ? P->n_slots_geom : (int)std::min<int64_t>(P->hdr()->n_geom, (int64_t)per_sm * P->ctx->sm_count);
+    }
+    kfn<<<P->band_grid, nthr, P->smem_band, s>>>(in, ws, P->band_wrows, P->band_wcols);
+    return cudaGetLastError();
+}
 template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
     if (P->use_coop) return launch_geom_coop(P, in, ws, s);
+    if (P->band_variant >= 0) return launch_geom_band(P, in, ws, s);
     auto kfn = P->geom_threads == 512 ? k_geom<NB, 512, 1> : P->geom_threads == 256 ? k_geom<NB, 256, 4> : k_geom<NB, 128, 8>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_geom);
     if (e != cudaSuccess) return e;
@@ -2154,7 +2308,7 @@ static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cuda
     const int nt = h->n_sets * h->n_freq;
     k_m0<<<(nt + 127) / 128, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
-    dim3 grid((unsigned)((P->max_FK + 127) / 128), (unsigned)h->n_sets);
+    dim3 grid((unsigned)((P->max_FK + 127) / 128), (unsigned)std::min(h->n_sets, 65535));
     k_mk<<<grid, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
     return MEEMB200_OK;
@@ -2167,6 +2321,7 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
         return fail(MEEMB200_EINVAL, "NULL output pointer");
     const BlobHeader* h = P->hdr();
     if (h->want_x && !out->x) return fail(MEEMB200_EINVAL, "plan was built with want_x but outputs.x is NULL");
+    DeviceGuard guard(P->ctx->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (!P->ev_ok) {
         for (auto& e : P->ev) CUDA_TRY(cudaEventCreate(&e));
@@ -2179,6 +2334,10 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
     CUDA_TRY(cudaEventRecord(P->ev[1], s));
     k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
+    if (out->c_vector) {
+        k_cvec<<<h->n_geom, 128, 0, s>>>(d_in, d_ws, out->c_vector);
+        CUDA_TRY(cudaGetLastError());
+    }
     if (h->algo != MEEMB200_ALGO_DENSE) {
         CUDA_TRY(P->nb_geom == 8 ? launch_geom<8>(P, d_in, d_ws, s) : P->nb_geom == 4 ? launch_geom<4>(P, d_in, d_ws, s) : launch_geom<2>(P, d_in, d_ws, s));
         if (h->algo == MEEMB200_ALGO_SCHUR) {
@@ -2252,13 +2411,16 @@ extern "C" int meemb200_phase_profile(meemb200_plan* P, const void* d_ws, double
 
 extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void* stream) {
     if (!P || !ho) return fail(MEEMB200_EINVAL, "NULL argument");
+    DeviceGuard guard(P->ctx->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const MeemPlanInfo& I = P->info;
     const size_t b_rr = 8 * (size_t)I.n_rr, b_r = 8 * (size_t)I.n_r, b_m0 = 8 * (size_t)I.n_sys, b_st = 4 * (size_t)I.n_sys, b_x = 16 * (size_t)I.n_x;
+    const size_t b_c = ho->c_vector ? 8 * (size_t)I.n_c : 0;
+    if (P->hdr()->want_x && !ho->x) return fail(MEEMB200_EINVAL, "plan was built with want_x but outputs.x is NULL");
     size_t off = 0;
     auto take = [&](size_t n) { size_t o = off; off = align_up(off + n, 256); return o; };
     const size_t o_in = take(I.input_bytes), o_ws = take(I.workspace_bytes), o_am = take(b_rr), o_dp = take(b_rr), o_f = take(b_r),
-                 o_p = take(b_r), o_m0 = take(b_m0), o_st = take(b_st), o_x = take(b_x);
+                 o_p = take(b_r), o_m0 = take(b_m0), o_st = take(b_st), o_x = take(b_x), o_c = take(b_c);
     char* base = nullptr;
     CUDA_TRY(cudaMallocAsync(reinterpret_cast<void**>(&base), off, s));
     MeemOutputs d;
@@ -2266,18 +2428,25 @@ extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void
     d.exc_force = reinterpret_cast<double*>(base + o_f); d.exc_phase = reinterpret_cast<double*>(base + o_p);
     d.m0 = reinterpret_cast<double*>(base + o_m0); d.status = reinterpret_cast<int32_t*>(base + o_st);
     d.x = I.n_x ? reinterpret_cast<double*>(base + o_x) : nullptr;
+    d.c_vector = b_c ? reinterpret_cast<double*>(base + o_c) : nullptr;
     cudaError_t e = cudaMemcpyAsync(base + o_in, P->blob.data(), I.input_bytes, cudaMemcpyHostToDevice, s);
     int rc = MEEMB200_OK;
     if (e != cudaSuccess) rc = fail(MEEMB200_ECUDA, cudaGetErrorString(e));
     if (!rc) rc = meemb200_solve(P, base + o_in, base + o_ws, I.workspace_bytes, &d, s);
     if (!rc) {
-        if (ho->added_mass) cudaMemcpyAsync(ho->added_mass, d.added_mass, b_rr, cudaMemcpyDeviceToHost, s);
-        if (ho->damping) cudaMemcpyAsync(ho->damping, d.damping, b_rr, cudaMemcpyDeviceToHost, s);
-        if (ho->exc_force) cudaMemcpyAsync(ho->exc_force, d.exc_force, b_r, cudaMemcpyDeviceToHost, s);
-        if (ho->exc_phase) cudaMemcpyAsync(ho->exc_phase, d.exc_phase, b_r, cudaMemcpyDeviceToHost, s);
-        if (ho->m0) cudaMemcpyAsync(ho->m0, d.m0, b_m0, cudaMemcpyDeviceToHost, s);
-        if (ho->status) cudaMemcpyAsync(ho->status, d.status, b_st, cudaMemcpyDeviceToHost, s);
-        if (ho->x && I.n_x) cudaMemcpyAsync(ho->x, d.x, b_x, cudaMemcpyDeviceToHost, s);
+        auto back = [&](void* dst, const void* src, size_t n) {
+            if (!dst || !n || rc) return;
+            const cudaError_t ce = cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, s);
+            if (ce != cudaSuccess) rc = fail(MEEMB200_ECUDA, std::string("solve_host download: ") + cudaGetErrorString(ce));
+        };
+        back(ho->added_mass, d.added_mass, b_rr);
+        back(ho->damping, d.damping, b_rr);
+        back(ho->exc_force, d.exc_force, b_r);
+        back(ho->exc_phase, d.exc_phase, b_r);
+        back(ho->m0, d.m0, b_m0);
+        back(ho->status, d.status, b_st);
+        back(ho->x, d.x, I.n_x ? b_x : 0);
+        back(ho->c_vector, d.c_vector, b_c);
     }
     cudaFreeAsync(base, s);
     e = cudaStreamSynchronize(s);
@@ -2291,6 +2460,7 @@ extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws,
     if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
     const BlobHeader* h = P->hdr();
     if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
+    DeviceGuard guard(P->ctx->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     int rc = enqueue_prologue(P, d_in, d_ws, s);
     if (rc) return rc;
@@ -2311,6 +2481,7 @@ extern "C" int meemb200_fields(meemb200_plan* P, const void* d_in, void* d_ws, s
     if (n_points < 1) return fail(MEEMB200_EINVAL, "n_points must be >= 1");
     const double fr = reinterpret_cast<const double*>(P->blob.data() + h->off_freq)[f];
     if (std::isinf(fr)) return fail(MEEMB200_EINVAL, "field evaluation needs a finite wavenumber");
+    DeviceGuard guard(P->ctx->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     int rc = enqueue_prologue(P, d_in, d_ws, s);
     if (rc) return rc;
@@ -2324,6 +2495,7 @@ extern "C" int meemb200_fields(meemb200_plan* P, const void* d_in, void* d_ws, s
 extern "C" int meemb200_roots(meemb200_ctx* ctx, int32_t n, int32_t K, const double* d_freq, const double* d_h, int32_t freq_kind,
                               int32_t root_mode, double* d_m0, double* d_mk, double* d_Nk, void* stream) {
     if (!ctx || n < 1 || K < 1 || !d_freq || !d_h || !d_m0 || !d_mk || !d_Nk) return fail(MEEMB200_EINVAL, "bad argument");
+    DeviceGuard guard(ctx->device);
     const int64_t t = (int64_t)n * K;
     k_roots_flat<<<(unsigned)((t + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(n, K, d_freq, d_h, freq_kind, root_mode, d_m0, d_mk, d_Nk);
     CUDA_TRY(cudaGetLastError());
@@ -2332,6 +2504,7 @@ extern "C" int meemb200_roots(meemb200_ctx* ctx, int32_t n, int32_t K, const dou
 
 extern "C" int meemb200_bessel(meemb200_ctx* ctx, int32_t kind, int64_t n, const double* d_x, double* d_out, void* stream) {
     if (!ctx || kind < 0 || kind > 7 || n < 1 || !d_x || !d_out) return fail(MEEMB200_EINVAL, "bad argument");
+    DeviceGuard guard(ctx->device);
     k_bessel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(kind, n, d_x, d_out);
     CUDA_TRY(cudaGetLastError());
     return MEEMB200_OK;
@@ -2339,6 +2512,7 @@ extern "C" int meemb200_bessel(meemb200_ctx* ctx, int32_t kind, int64_t n, const
 
 extern "C" int meemb200_fp64_peak(meemb200_ctx* ctx, int32_t kind, double* flops, void* stream) {
     if (!ctx || !flops) return fail(MEEMB200_EINVAL, "bad argument");
+    DeviceGuard guard(ctx->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int blocks = ctx->sm_count * 8, threads = 256, iters = 1 << 15;
     double* buf = nullptr;

@@ -35,15 +35,15 @@ MEEM_HD void fnma(cplx& acc, cplx a, cplx b) {
 MEEM_HD bool finite_of(double a) { return isfinite(a); }
 MEEM_HD bool finite_of(cplx a) { return isfinite(a.re) && isfinite(a.im); }
 
-template <class T, int NB>
+template <class T, int NB, int CHUNK = kLuChunk>
 __host__ __device__ constexpr size_t lu_smem_bytes(int max_rows) {
-    return sizeof(T) * (size_t)NB * ((size_t)max_rows + kLuChunk) + 16 * sizeof(int);
+    return sizeof(T) * (size_t)NB * ((size_t)max_rows + CHUNK) + 16 * sizeof(int);
 }
 
 #ifdef __CUDACC__
 
-// W[i][c] -= sum_q Lp[q*lstride + (i - row0)] * Us[q*kLuChunk + (c - c0)]  for i in [r_begin, r_end), c in [c0, c1)
-template <class T, int NB, bool SMALL = false>
+// W[i][c] -= sum_q Lp[q*lstride + (i - row0)] * Us[q*CHUNK + (c - c0)]  for i in [r_begin, r_end), c in [c0, c1)
+template <class T, int NB, bool SMALL = false, int CHUNK = kLuChunk>
 __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, const T* Lp, int lstride,
                                int c0, int c1, const T* Us, int nbj) {
     constexpr int TR = LuTile<T, SMALL>::TR, TC = LuTile<T, SMALL>::TC;
@@ -83,7 +83,7 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
 #pragma unroll
                 for (int c = 0; c < TC; ++c) fnma(acc[r][c], l[r], u[c]);
             lp += lstride;
-            up += kLuChunk;
+            up += CHUNK;
         };
         if (nbj == NB) {
 #pragma unroll
@@ -107,17 +107,21 @@ __device__ void lu_rank_update(T* W, long ld, int r_begin, int r_end, int row0, 
 // (nrows >= npiv; columns >= npiv ride along as right-hand sides).  On return rows [0, npiv) hold
 // U and the transformed right-hand sides; rows >= npiv hold the Schur remainder in columns >= npiv.
 // status: bit 0 set on an exactly-zero pivot, bit 1 on a non-finite pivot column.
-// smem: lu_smem_bytes<T,NB>(nrows).  All threads of the CTA must call.
-template <class T, int NB, bool SMALL = false>
-__device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsigned char* smem_raw, int* status) {
+// smem: lu_smem_bytes<T,NB,CHUNK>(nrows).  All threads of the CTA must call.
+// nsearch (default nrows): only rows < nsearch are pivot candidates; rows in [nsearch, nrows) are eliminated like every
+// other row but never become a pivot row (the c rows of the window elimination, k_geom_band).
+template <class T, int NB, bool SMALL = false, int CHUNK = kLuChunk>
+__device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsigned char* smem_raw, int* status, int nsearch = -1) {
     T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][nrows] column-major
-    T* ust = panel + (size_t)NB * nrows;                     // [NB][kLuChunk]
-    int* piv = reinterpret_cast<int*>(ust + (size_t)NB * kLuChunk);
+    T* ust = panel + (size_t)NB * nrows;                     // [NB][CHUNK]
+    int* piv = reinterpret_cast<int*>(ust + (size_t)NB * CHUNK);
+    if (nsearch < 0) nsearch = nrows;
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5;
     for (int k0 = 0; k0 < npiv; k0 += NB) {
         const int nbj = min(NB, npiv - k0);
         const int rows = nrows - k0;
+        const int srows = nsearch - k0;
         // stage the panel
         for (int idx = tid; idx < rows * nbj; idx += nthr) {
             const int i = idx / nbj, q = idx - i * nbj;
@@ -128,7 +132,7 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
             for (int j = 0; j < nbj; ++j) {
                 double best = -1.0;
                 int bi = 0x7fffffff;
-                for (int i = j + lane; i < rows; i += 32) {
+                for (int i = j + lane; i < srows; i += 32) {
                     const double v = cabs1(panel[j * nrows + i]);
                     if (v > best) { best = v; bi = i; }
                 }
@@ -140,7 +144,7 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
                 }
                 best = __shfl_sync(0xffffffffu, best, 0);
                 bi = __shfl_sync(0xffffffffu, bi, 0);
-                if (bi >= rows) bi = j;                       // column of NaNs
+                if (bi >= srows) bi = j;                      // column of NaNs
                 if (lane == 0) {
                     piv[j] = k0 + bi;
                     if (!(best < INFINITY) || best < 0.0) atomicOr(status, 2);
@@ -168,8 +172,8 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
             W[(long)(k0 + i) * ld + k0 + q] = panel[q * nrows + i];
         }
         const int cr0 = k0 + nbj;
-        for (int cc0 = cr0; cc0 < ncols; cc0 += kLuChunk) {
-            const int cc1 = min(ncols, cc0 + kLuChunk);
+        for (int cc0 = cr0; cc0 < ncols; cc0 += CHUNK) {
+            const int cc1 = min(ncols, cc0 + CHUNK);
             // row swaps + U12 = L11^{-1} A12, one column per thread
             for (int c = cc0 + tid; c < cc1; c += nthr) {
                 T u[NB];
@@ -193,12 +197,12 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
                             if (q2 < q) fnma(v, panel[q2 * nrows + q], u[q2]);
                         u[q] = v;
                         W[(long)(k0 + q) * ld + c] = v;
-                        ust[q * kLuChunk + (c - cc0)] = v;
+                        ust[q * CHUNK + (c - cc0)] = v;
                     }
                 }
             }
             __syncthreads();
-            lu_rank_update<T, NB, SMALL>(W, ld, k0 + nbj, nrows, k0, panel, nrows, cc0, cc1, ust, nbj);
+            lu_rank_update<T, NB, SMALL, CHUNK>(W, ld, k0 + nbj, nrows, k0, panel, nrows, cc0, cc1, ust, nbj);
             __syncthreads();
         }
     }
@@ -206,7 +210,7 @@ __device__ void lu_forward(T* W, long ld, int nrows, int npiv, int ncols, unsign
 
 // Back-substitution U X = Y for right-hand-side columns [c0, c1) after lu_forward (U = rows/cols
 // [0, npiv)); X overwrites Y.  Blocked bottom-up, reusing the rank-NB update for the rows above.
-template <class T, int NB, bool SMALL = false>
+template <class T, int NB, bool SMALL = false, int CHUNK = kLuChunk>
 __device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned char* smem_raw, int max_rows) {
     T* panel = reinterpret_cast<T*>(smem_raw);               // [NB][max_rows]: U[0:k0+nbj, k0:k0+nbj]
     T* ust = panel + (size_t)NB * max_rows;
@@ -221,8 +225,8 @@ __device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned ch
             panel[q * max_rows + i] = W[(long)i * ld + k0 + q];
         }
         __syncthreads();
-        for (int cc0 = c0; cc0 < c1; cc0 += kLuChunk) {
-            const int cc1 = min(c1, cc0 + kLuChunk);
+        for (int cc0 = c0; cc0 < c1; cc0 += CHUNK) {
+            const int cc1 = min(c1, cc0 + CHUNK);
             for (int c = cc0 + tid; c < cc1; c += nthr) {
                 T x[NB];
 #pragma unroll
@@ -235,12 +239,12 @@ __device__ void lu_backward(T* W, long ld, int npiv, int c0, int c1, unsigned ch
                         v = v / panel[q * max_rows + k0 + q];
                         x[q] = v;
                         W[(long)(k0 + q) * ld + c] = v;
-                        ust[q * kLuChunk + (c - cc0)] = v;
+                        ust[q * CHUNK + (c - cc0)] = v;
                     }
                 }
             }
             __syncthreads();
-            lu_rank_update<T, NB, SMALL>(W, ld, 0, k0, 0, panel, max_rows, cc0, cc1, ust, nbj);
+            lu_rank_update<T, NB, SMALL, CHUNK>(W, ld, 0, k0, 0, panel, max_rows, cc0, cc1, ust, nbj);
             __syncthreads();
         }
     }
