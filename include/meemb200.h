@@ -12,6 +12,7 @@
  *                          build_problem_cache + assemble_A_multi / assemble_b_multi
  *                          (meem_engine.py:44-63, :100-305), scipy.linalg.lu_factor / lu_solve
  *                          (:609, :633), compute_hydrodynamic_coefficients (:326-393)
+ *   meemb200_coefficients  MEEMEngine.compute_hydrodynamic_coefficients for a caller-supplied X (:326-393)
  *   meemb200_assemble      MEEMEngine.assemble_A_multi / assemble_b_multi (meem_engine.py:44-63),
  *                          assemble_c_multi (:65-98) — for A/b parity tests
  *   meemb200_roots         wavenumber + _ensure_m_k_and_N_k_arrays (meem_engine.py:33-42)
@@ -86,6 +87,11 @@ typedef struct MeemPlanInfo {
     int64_t n_x;              /* total complex elements of X = sum_g F * R_g * NT_g (0 unless want_x) */
     int64_t n_launches;       /* kernel launches one meemb200_solve enqueues */
     double flops;             /* real FP64 flops of the dense-matrix kernels one solve executes (closed form) */
+    int64_t n_c;              /* total elements of c_vector = sum_g R_g * p_g (frequency independent) */
+    int32_t geom_kernel;      /* geometry-stage kernel the plan chose: 0 dense LU per CTA (k_geom), 1 grid-cooperative dense LU
+                               * (k_geom_coop), 2/3/4 window elimination (k_geom_band: small shared-memory window / shared-memory
+                               * window / global-slot window), -1 none (ALGO_DENSE) */
+    int32_t reserved;
 } MeemPlanInfo;
 
 /* Device output pointers (caller-owned).  Layouts are the reference's (meem_engine.py:573-580):
@@ -98,6 +104,9 @@ typedef struct MeemOutputs {
     double* m0;               /* [g][f] wavenumber used */
     int32_t* status;          /* [g][f] 0 ok, 1 singular pivot, 2 non-finite */
     double* x;                /* optional [g][f][i][NT_g] complex128 (re,im interleaved), may be NULL */
+    double* c_vector;         /* optional [g][j][p_g] real: the c vector of mode j (meem_engine.py:65-98, :390, :646-652).  It does
+                               * not depend on the frequency and its imaginary part is 0: the host broadcasts it to the
+                               * reference's (frequency, mode, p) complex layout (results.py:243-248).  May be NULL */
 } MeemOutputs;
 
 typedef struct meemb200_ctx meemb200_ctx;
@@ -117,8 +126,8 @@ int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* batch, meemb200_pla
 int meemb200_plan_destroy(meemb200_plan* plan);
 int meemb200_plan_info(const meemb200_plan* plan, MeemPlanInfo* info);
 const void* meemb200_plan_blob(const meemb200_plan* plan);
-/* element offsets of geometry g: out[0]=rr, out[1]=r, out[2]=sys, out[3]=x, out[4]=NT, out[5]=p */
-int meemb200_plan_offsets(const meemb200_plan* plan, int32_t g, int64_t out[6]);
+/* element offsets of geometry g: out[0]=rr, out[1]=r, out[2]=sys, out[3]=x, out[4]=NT, out[5]=p, out[6]=c_vector, out[7]=R */
+int meemb200_plan_offsets(const meemb200_plan* plan, int32_t g, int64_t out[8]);
 /* overwrite the frequency grid inside the packed blob (same n_freq), e.g. for the next sweep */
 int meemb200_plan_set_freq(meemb200_plan* plan, const double* freq);
 
@@ -138,6 +147,16 @@ int meemb200_solve_host(meemb200_plan* plan, const MeemOutputs* host_out, void* 
  * Any of A/b/c may be NULL. */
 int meemb200_assemble(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
                       int32_t g, int32_t f, double* d_A, double* d_b, double* d_c, void* stream);
+/* The coupling table I_mk (multi_equations.py:96-124; table build meem_engine.py:136-141) of system (g, f) exactly as the
+ * product frequency stage computes it (angle-addition form, sinc series near resonances - not the reference-ordered form
+ * that meemb200_assemble uses): d_out[N][K] row-major, reference index order.  Parity export. */
+int meemb200_imk_table(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
+                       int32_t g, int32_t f, double* d_out, void* stream);
+/* Reduction of ONE given solution X ([NT] complex128, device) of system (g, f) to what
+ * MEEMEngine.compute_hydrodynamic_coefficients returns per mode j (meem_engine.py:326-393):
+ * d_out[j][0..3] = real (added mass), imag (damping), excitation_phase, excitation_force, j over the plan's modes. */
+int meemb200_coefficients(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
+                          int32_t g, int32_t f, const double* d_X, double* d_out, void* stream);
 /* Potential and velocity fields of one solution at n_points points (device pointers): replaces the arithmetic of
  * MEEMEngine.calculate_potentials / calculate_velocities (meem_engine.py:395-467, :478-553).  X: [NT] complex128
  * solution of geometry g at frequency index f for radiating mode `mode` (its heaving flags select the particular

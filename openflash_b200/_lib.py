@@ -32,14 +32,15 @@ class MeemPlanInfo(C.Structure):
     _fields_ = [
         ("input_bytes", C.c_size_t), ("workspace_bytes", C.c_size_t),
         ("n_rr", C.c_int64), ("n_r", C.c_int64), ("n_sys", C.c_int64), ("n_x", C.c_int64),
-        ("n_launches", C.c_int64), ("flops", C.c_double),
+        ("n_launches", C.c_int64), ("flops", C.c_double), ("n_c", C.c_int64),
+        ("geom_kernel", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
 class MeemOutputs(C.Structure):
     _fields_ = [
         ("added_mass", C.c_void_p), ("damping", C.c_void_p), ("exc_force", C.c_void_p), ("exc_phase", C.c_void_p),
-        ("m0", C.c_void_p), ("status", C.c_void_p), ("x", C.c_void_p),
+        ("m0", C.c_void_p), ("status", C.c_void_p), ("x", C.c_void_p), ("c_vector", C.c_void_p),
     ]
 
 
@@ -53,7 +54,7 @@ EXPORTS = [
     "meemb200_version", "meemb200_last_error", "meemb200_create", "meemb200_destroy", "meemb200_sm_count",
     "meemb200_plan_create", "meemb200_plan_destroy", "meemb200_plan_info", "meemb200_plan_blob",
     "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_solve", "meemb200_solve_host",
-    "meemb200_assemble", "meemb200_fields", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
+    "meemb200_assemble", "meemb200_imk_table", "meemb200_coefficients", "meemb200_fields", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
     "meemb200_debug_layout",
 ]
 
@@ -84,6 +85,8 @@ def load():
     lib.meemb200_solve.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(MeemOutputs), vp]
     lib.meemb200_solve_host.argtypes = [vp, C.POINTER(MeemOutputs), vp]
     lib.meemb200_assemble.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp, vp, vp]
+    lib.meemb200_imk_table.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp]
+    lib.meemb200_coefficients.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp, vp]
     lib.meemb200_fields.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int64, vp, vp, vp, vp]
     lib.meemb200_roots.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, vp]
     lib.meemb200_bessel.argtypes = [vp, C.c_int32, C.c_int64, vp, vp, vp]

@@ -65,6 +65,68 @@ class FlatGeometry:
         return cls(h, a, d, NMK, flags)
 
 
+def output_layout(F, R, NT, K, want_c=False, want_x=False):
+    """Byte layout of the packed output buffer of a batch: {name: (offset, nbytes)}, total bytes.  R, NT, K are the
+    per-geometry mode counts, system sizes and exterior mode counts.  Pure host arithmetic: every rank of a sharded
+    solve can compute every other rank's layout (openflash_b200.distributed)."""
+    R = np.asarray(R, dtype=np.int64)
+    NT = np.asarray(NT, dtype=np.int64)
+    K = np.asarray(K, dtype=np.int64)
+    n_rr, n_r, n_sys = int(F * (R * R).sum()), int(F * R.sum()), int(F * len(R))
+    segs = [("added_mass", 8 * n_rr), ("damping", 8 * n_rr), ("excitation_force", 8 * n_r),
+            ("excitation_phase", 8 * n_r), ("m0", 8 * n_sys), ("status", 4 * n_sys)]
+    if want_c:
+        segs.append(("c_vector", 8 * int((R * (NT - K)).sum())))
+    if want_x:
+        segs.append(("X", 16 * int(F * (R * NT).sum())))
+    seg, off = {}, 0
+    for name, nbytes in segs:
+        seg[name] = (off, nbytes)
+        off = (off + nbytes + 255) & ~255
+    return seg, max(off, 256)
+
+
+def unpack_outputs(buf, seg, G, F, want_c=False, want_x=False, copy=True):
+    """Flat numpy arrays out of a packed output buffer (uint8 numpy array) with layout `seg`."""
+    def arr(name, dtype):
+        off, nbytes = seg[name]
+        a = buf[off:off + nbytes].view(dtype)
+        return a.copy() if copy else a
+    out = dict(added_mass=arr("added_mass", np.float64), damping=arr("damping", np.float64),
+               excitation_force=arr("excitation_force", np.float64), excitation_phase=arr("excitation_phase", np.float64),
+               m0=arr("m0", np.float64).reshape(G, F), status=arr("status", np.int32).reshape(G, F))
+    if want_c:
+        out["c_vector"] = arr("c_vector", np.float64)
+    if want_x:
+        out["X"] = arr("X", np.complex128)
+    return out
+
+
+def split_outputs(flat, F, R, NT, K, want_c=False, want_x=False):
+    """Per-geometry views with the reference's shapes: added_mass[F,R,R] (force on j, motion of i), ..."""
+    R64 = np.asarray(R, dtype=np.int64)
+    NT = np.asarray(NT, dtype=np.int64)
+    K = np.asarray(K, dtype=np.int64)
+    off_rr = np.concatenate([[0], np.cumsum(F * R64 * R64)])
+    off_r = np.concatenate([[0], np.cumsum(F * R64)])
+    off_x = np.concatenate([[0], np.cumsum(F * R64 * NT)])
+    off_c = np.concatenate([[0], np.cumsum(R64 * (NT - K))])
+    res = []
+    for g in range(len(R64)):
+        Rg = int(R64[g])
+        r = dict(added_mass=flat["added_mass"][off_rr[g]:off_rr[g + 1]].reshape(F, Rg, Rg),
+                 damping=flat["damping"][off_rr[g]:off_rr[g + 1]].reshape(F, Rg, Rg),
+                 excitation_force=flat["excitation_force"][off_r[g]:off_r[g + 1]].reshape(F, Rg),
+                 excitation_phase=flat["excitation_phase"][off_r[g]:off_r[g + 1]].reshape(F, Rg),
+                 m0=flat["m0"][g], status=flat["status"][g])
+        if want_x:
+            r["X"] = flat["X"][off_x[g]:off_x[g + 1]].reshape(F, Rg, int(NT[g]))
+        if want_c:      # [R, p]: c vector of every radiating mode (frequency independent, meem_engine.py:65-98)
+            r["c_vector"] = flat["c_vector"][off_c[g]:off_c[g + 1]].reshape(Rg, -1)
+        res.append(r)
+    return res
+
+
 _contexts = {}
 
 
@@ -82,7 +144,8 @@ class BatchPlan:
     """A validated, packed batch plus its device buffers; ``solve()`` may be called repeatedly."""
 
     def __init__(self, geometries: Sequence[FlatGeometry], freqs, *, freq_kind=FREQ_OMEGA, algo=ALGO_SCHUR,
-                 root_mode=ROOTS_REFERENCE, want_x=False, rho: Optional[float] = None, device: int = 0):
+                 root_mode=ROOTS_REFERENCE, want_x=False, want_c=False, rho: Optional[float] = None, device: int = 0,
+                 out_bytes_min: int = 0):
         import torch
         self.torch = torch
         self.lib = _lib.load()
@@ -99,6 +162,7 @@ class BatchPlan:
         self.M = np.array([g.M for g in geometries], dtype=np.int32)
         self.NT = np.array([g.size for g in geometries], dtype=np.int64)
         self.want_x = bool(want_x)
+        self.want_c = bool(want_c)
         self.algo = int(algo)
         reg_off = np.zeros(self.G + 1, dtype=np.int32)
         np.cumsum(self.M + 1, out=reg_off[1:])
@@ -136,29 +200,24 @@ class BatchPlan:
         self.plan = plan
         self.info = _lib.MeemPlanInfo()
         _lib.check(self.lib.meemb200_plan_info(self.plan, C.byref(self.info)))
-        Fq = self.F
-        R64 = self.R.astype(np.int64)
-        self.off_rr = np.concatenate([[0], np.cumsum(Fq * R64 * R64)])
-        self.off_r = np.concatenate([[0], np.cumsum(Fq * R64)])
-        self.off_x = np.concatenate([[0], np.cumsum(Fq * R64 * self.NT)]) if self.want_x else None
-        # device buffers (torch tensors as plain memory) and the pinned staging copy of the inputs
+        # device buffers (torch tensors as plain memory) and the pinned staging copy of the inputs.  Every output lives
+        # in ONE device buffer (segments 256-byte aligned) mirrored by ONE pinned host buffer, so download() is a single
+        # device->host copy at full link speed instead of one pageable copy per array.
         nb = int(self.info.input_bytes)
         self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
         self._refresh_host_blob()
+        self.K = np.array([int(g.NMK[-1]) for g in geometries], dtype=np.int64)
+        self._seg, self._out_bytes = output_layout(self.F, self.R, self.NT, self.K, self.want_c, self.want_x)
+        self._out_bytes = max(self._out_bytes, int(out_bytes_min))
         with torch.cuda.device(self.device):
             self.d_blob = torch.empty(nb, dtype=torch.uint8, device=self.device)
             self.d_ws = torch.empty(int(self.info.workspace_bytes), dtype=torch.uint8, device=self.device)
-            f64 = torch.float64
-            self.d_am = torch.empty(int(self.info.n_rr), dtype=f64, device=self.device)
-            self.d_dp = torch.empty(int(self.info.n_rr), dtype=f64, device=self.device)
-            self.d_force = torch.empty(int(self.info.n_r), dtype=f64, device=self.device)
-            self.d_phase = torch.empty(int(self.info.n_r), dtype=f64, device=self.device)
-            self.d_m0 = torch.empty(int(self.info.n_sys), dtype=f64, device=self.device)
-            self.d_status = torch.empty(int(self.info.n_sys), dtype=torch.int32, device=self.device)
-            self.d_x = torch.empty(2 * int(self.info.n_x), dtype=f64, device=self.device) if self.want_x else None
-        self.out = _lib.MeemOutputs(self.d_am.data_ptr(), self.d_dp.data_ptr(), self.d_force.data_ptr(),
-                                    self.d_phase.data_ptr(), self.d_m0.data_ptr(), self.d_status.data_ptr(),
-                                    self.d_x.data_ptr() if self.want_x else None)
+            self.d_out = torch.empty(self._out_bytes, dtype=torch.uint8, device=self.device)
+        self.h_out = torch.empty(self._out_bytes, dtype=torch.uint8, pin_memory=True)
+        base = self.d_out.data_ptr()
+        ptr = lambda name: (base + self._seg[name][0]) if name in self._seg else None  # noqa: E731
+        self.out = _lib.MeemOutputs(ptr("added_mass"), ptr("damping"), ptr("excitation_force"), ptr("excitation_phase"),
+                                    ptr("m0"), ptr("status"), ptr("X"), ptr("c_vector"))
         self._uploaded = False
 
     def _refresh_host_blob(self):
@@ -181,7 +240,8 @@ class BatchPlan:
 
     @property
     def d2h_bytes(self):
-        return int(16 * self.info.n_rr + 16 * self.info.n_r + 12 * self.info.n_sys + 16 * self.info.n_x)
+        return int(16 * self.info.n_rr + 16 * self.info.n_r + 12 * self.info.n_sys + 16 * self.info.n_x
+                   + (8 * self.info.n_c if self.want_c else 0))
 
     def set_frequencies(self, freqs):
         freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
@@ -234,17 +294,23 @@ class BatchPlan:
         _lib.check(self.lib.meemb200_phase_profile(self.plan, self.d_ws.data_ptr(), cyc, C.c_void_p(stream)))
         return int(cyc[1])
 
-    def download(self):
-        """Device->host read of all outputs; returns flat numpy arrays."""
+    def _view(self, buf, name, dtype):
+        off, nbytes = self._seg[name]
+        return buf[off:off + nbytes].view(dtype)
+
+    def device_output(self, name):
+        """Device-resident view (torch tensor) of one output array of the last solve: 'added_mass', 'damping',
+        'excitation_force', 'excitation_phase', 'm0' (float64), 'status' (int32), 'c_vector', 'X' when requested."""
         t = self.torch
-        out = dict(added_mass=self.d_am.cpu().numpy(), damping=self.d_dp.cpu().numpy(),
-                   excitation_force=self.d_force.cpu().numpy(), excitation_phase=self.d_phase.cpu().numpy(),
-                   m0=self.d_m0.cpu().numpy().reshape(self.G, self.F),
-                   status=self.d_status.cpu().numpy().reshape(self.G, self.F))
-        if self.want_x:
-            out["X"] = self.d_x.cpu().numpy().view(np.complex128)
+        return self._view(self.d_out, name, t.int32 if name == "status" else t.float64)
+
+    def download(self, copy=True):
+        """ONE device->host copy of all outputs into the plan's pinned buffer; returns flat numpy arrays
+        (copies by default; ``copy=False`` returns views of the pinned buffer, valid until the next download)."""
+        t = self.torch
+        self.h_out.copy_(self.d_out, non_blocking=True)
         t.cuda.current_stream(self.device).synchronize()
-        return out
+        return unpack_outputs(self.h_out.numpy(), self._seg, self.G, self.F, self.want_c, self.want_x, copy)
 
     def run(self):
         self.upload()
@@ -253,20 +319,7 @@ class BatchPlan:
 
     def split(self, flat):
         """Per-geometry views with the reference's shapes: added_mass[F,R,R] (force on j, motion of i), ..."""
-        res = []
-        F = self.F
-        for g in range(self.G):
-            R = int(self.R[g])
-            r = dict(
-                added_mass=flat["added_mass"][self.off_rr[g]:self.off_rr[g + 1]].reshape(F, R, R),
-                damping=flat["damping"][self.off_rr[g]:self.off_rr[g + 1]].reshape(F, R, R),
-                excitation_force=flat["excitation_force"][self.off_r[g]:self.off_r[g + 1]].reshape(F, R),
-                excitation_phase=flat["excitation_phase"][self.off_r[g]:self.off_r[g + 1]].reshape(F, R),
-                m0=flat["m0"][g], status=flat["status"][g])
-            if self.want_x:
-                r["X"] = flat["X"][self.off_x[g]:self.off_x[g + 1]].reshape(F, R, int(self.NT[g]))
-            res.append(r)
-        return res
+        return split_outputs(flat, self.F, self.R, self.NT, self.K, self.want_c, self.want_x)
 
     # -- parity / debugging exports ---------------------------------------------------------------
     def assemble(self, g=0, f=0):
@@ -288,6 +341,47 @@ class BatchPlan:
                 b.cpu().numpy().view(np.complex128).reshape(R, NT),
                 np.ascontiguousarray(cc[:, :p]), cc[:, p].real.copy())
 
+
+    def imk_table(self, g=0, f=0):
+        """The product frequency stage's coupling table I_mk [N, K] of system (g, f) (parity export)."""
+        t = self.torch
+        if not self._uploaded:
+            self.upload()
+        nmk = self._keep[4][self._keep[0][g]:self._keep[0][g + 1]]
+        N, K = int(nmk[-2]), int(nmk[-1])
+        out = t.empty(N * K, dtype=t.float64, device=self.device)
+        stream = t.cuda.current_stream(self.device).cuda_stream
+        rc = self.lib.meemb200_imk_table(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(), int(self.info.workspace_bytes),
+                                         int(g), int(f), out.data_ptr(), C.c_void_p(stream))
+        if rc == -1:
+            raise ValueError(self.lib.meemb200_last_error().decode())
+        _lib.check(rc)
+        return out.cpu().numpy().reshape(N, K)
+
+    GEOM_KERNELS = {-1: "none", 0: "k_geom", 1: "k_geom_coop", 2: "k_geom_band<smem,128>", 3: "k_geom_band<smem,256>",
+                    4: "k_geom_band<global,512>"}
+
+    @property
+    def geom_kernel(self):
+        return self.GEOM_KERNELS[int(self.info.geom_kernel)]
+
+    def coefficients(self, X, g=0, f=0):
+        """compute_hydrodynamic_coefficients for a caller-supplied solution X ([NT] complex) of system (g, f): array
+        [R, 4] = real, imag, excitation_phase, excitation_force per mode j of the plan (meem_engine.py:326-393)."""
+        t = self.torch
+        if not self._uploaded:
+            self.upload()
+        Xc = np.ascontiguousarray(np.asarray(X, dtype=np.complex128).ravel())
+        if Xc.size != int(self.NT[g]):
+            raise ValueError("X must have N_T entries")
+        d_X = t.from_numpy(Xc.view(np.float64).copy()).to(self.device)
+        R = int(self.R[g])
+        out = t.empty(4 * R, dtype=t.float64, device=self.device)
+        stream = t.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.meemb200_coefficients(self.plan, self.d_blob.data_ptr(), self.d_ws.data_ptr(),
+                                                  int(self.info.workspace_bytes), int(g), int(f), d_X.data_ptr(),
+                                                  out.data_ptr(), C.c_void_p(stream)))
+        return out.cpu().numpy().reshape(R, 4)
 
     def fields(self, X, r, z, g=0, f=0, mode=0):
         """Raw field values of solution X ([NT] complex) of system (g, f), radiating mode `mode`, at points (r, z):

@@ -154,6 +154,54 @@ __global__ void k_cvec(const void* blob, void* ws, double* out) {
                        out + gd.out_c + (int64_t)j * gd.p, threadIdx.x, blockDim.x);
 }
 
+__device__ __forceinline__ double warp_sum_all(double v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+// Reduction of ONE given solution X (N_T complex) of system (g, f) to the reference's per-mode dicts
+// (compute_hydrodynamic_coefficients, meem_engine.py:326-393): out[j][0..3] = real (added mass), imag (damping),
+// excitation phase, excitation force for every radiating mode j of the plan's geometry.  One warp per mode.
+__global__ void k_reduce(const void* blob, void* ws, int gi, int f, const cplx* X, double* out) {
+    DevView v = make_view(blob, ws);
+    __shared__ Layout L;
+    const GeomDesc gd = v.geom[gi];
+    const Geom g = geom_of(v, gd);
+    if (threadIdx.x == 0) make_layout(g, L);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const RootSet rs = v.sets[gd.root_set];
+    const double m0 = v.roots[rs.off + f];
+    const double* tab = v.tables + gd.tab_off;
+    const int M = gd.M;
+    for (int j = warp; j < gd.R; j += nwarp) {
+        const uint8_t* hv = v.flags + gd.flag_off + (int64_t)j * (M + 1);
+        double re = 0.0, im = 0.0;
+        for (int i = 0; i < M; ++i) {
+            if (!hv[i]) continue;
+            const int N = g.nmk[i];
+            for (int n = lane; n < (i == 0 ? 1 : 2) * N; n += 32) {
+                const double c = tab[L.tab[i] + 8 * N + n];          // int_R1 * z_n | int_R2 * z_n
+                const cplx x = X[L.col[i] + n];
+                re = fma(c, x.re, re); im = fma(c, x.im, im);
+            }
+        }
+        re = warp_sum_all(re); im = warp_sum_all(im);
+        if (lane == 0) {
+            const bool inf_m0 = isinf(m0);
+            const double phi = phi_sum(g, L, tab, hv);
+            const double cre = 2.0 * kPi * (re + phi), cim = 2.0 * kPi * im;
+            const double dpv = inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+            const cplx xe = X[gd.p];
+            out[4 * j + 0] = cre * v.hdr->rho;
+            out[4 * j + 1] = dpv;
+            out[4 * j + 2] = inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xe.im, xe.re) - hankel0_angle(m0 * g.a[M - 1]);
+            out[4 * j + 3] = excitation_force(dpv, m0, g.h, kRhoDefault);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // roots
 __global__ void k_m0(const void* blob, void* ws) {
@@ -949,6 +997,125 @@ enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, 
 #define PHASE_END_S(ph) PHASE_END(ph)
 #endif
 
+// Coupling table I_mk of one (geometry, frequency) system as the frequency stage consumes it: Imk[row][kp] with
+// column kp = exterior mode kp + 1 (the propagating mode k = 0 is carried LAST, kp = K - 1) and row kk = harmonic
+// perm[kk] of the last interior region (perm == nullptr: identity).  All threads of the CTA must call; sm needs
+// 4K + 3N doubles for the angle-addition form (else every entry goes through the reference-ordered imk()).
+// Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
+//   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
+// with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
+// sines, four divisions and a square root.  Both forms carry ~1e-13 absolute argument-rounding noise in the
+// sines (|theta| eps, theta up to ~1e3); the exact-equality branch |m_k| == lambda is kept.  Row m = 0 and
+// column k = 0 go through the reference-ordered imk().  (meemb200_assemble keeps imk() for every entry.)
+__device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* mk, const double* Nk, int N, int K, int ldk,
+                              const int* perm, double* Imk, double* sm, int sm_doubles, int* sh_row0) {
+    const int tid = threadIdx.x, nthr = blockDim.x;
+#define HARM(kk) (perm ? perm[kk] : (kk))
+    const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= sm_doubles;
+    if (fast) {
+        double* tmk = sm;               // [K] m_k (permuted)
+        double* tsk = tmk + K;          // sin(m_k L)
+        double* tck = tsk + K;          // cos(m_k L)
+        double* tnk = tck + K;          // sqrt(2 / N_k) / 2
+        double* tlm = tnk + K;          // [N] lambda_m
+        double* tsl = tlm + N;          // sin(lambda_m L)
+        double* tcl = tsl + N;          // cos(lambda_m L)
+        const double Lh = g.h - g.d[g.M - 1];
+        for (int kp = tid; kp < K; kp += nthr) {
+            const int k = (kp == K - 1) ? 0 : kp + 1;
+            const double mv = mk[k];
+            double sv, cv;
+            const double pr = mv * Lh, er = fma(mv, Lh, -pr);     // exact product = pr + er
+            sincos(pr, &sv, &cv);
+            tmk[kp] = mv; tsk[kp] = fma(er, cv, sv); tck[kp] = fma(-er, sv, cv);
+            tnk[kp] = sqrt(2.0 / Nk[k]) * 0.5;
+        }
+        for (int n = tid; n < N; n += nthr) {
+            const double lam = lambda_ni(HARM(n), g.M - 1, g);
+            double sv, cv;
+            const double pr = lam * Lh, er = fma(lam, Lh, -pr);
+            sincos(pr, &sv, &cv);
+            tlm[n] = lam; tsl[n] = fma(er, cv, sv); tcl[n] = fma(-er, sv, cv);
+        }
+        __syncthreads();
+        // row m = 0 and column k = 0 (reference-ordered forms), kept out of the main loop so that it stays uniform
+        for (int e = tid; e < N * 2; e += nthr) {                 // column k = 0 of every row; find the row of harmonic 0
+            const int kk = e >> 1;
+            if (e & 1) { if (HARM(kk) == 0) (*sh_row0) = kk; }
+            else Imk[(long)kk * ldk + K - 1] = imk(HARM(kk), 0, g, ex, mk, Nk);
+        }
+        __syncthreads();
+        for (int kp = tid; kp < K - 1; kp += nthr) Imk[(long)(*sh_row0) * ldk + kp] = imk(0, kp + 1, g, ex, mk, Nk);
+        // interior: one row per warp, lanes over the columns, branch-free except the exact-equality case.
+        //   (a + b) / sp + S / sd  over the common denominator, S = sin(sd L):  a - b away from a resonance,
+        //   x sinc(x) (Taylor, |x| = |sd L| < 1) near one, where a - b would lose digits to cancellation
+        {
+            const int lane_ = tid & 31, warp_ = tid >> 5, nwarp_ = nthr >> 5;
+            for (int n = warp_; n < N; n += nwarp_) {
+                if (n == (*sh_row0)) continue;
+                const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
+                double* row = Imk + (long)n * ldk;
+                for (int kp = lane_; kp < K - 1; kp += 32) {
+                    const double mv = tmk[kp];
+                    const double a = tsk[kp] * cl, b = tck[kp] * sl;
+                    const double sp = mv + lam, sd = mv - lam;
+                    const double x = sd * Lh, x2 = x * x;
+                    double S = a - b;
+                    if (fabs(x) < 1.0) {
+                        double pl = -8.22063524662432972e-18;                       // -1/19!
+                        pl = fma(pl, x2, 2.81145725434552076e-15);                  //  1/17!
+                        pl = fma(pl, x2, -7.64716373181981648e-13);                 // -1/15!
+                        pl = fma(pl, x2, 1.60590438368216146e-10);                  //  1/13!
+                        pl = fma(pl, x2, -2.50521083854417188e-08);                 // -1/11!
+                        pl = fma(pl, x2, 2.75573192239858907e-06);                  //  1/9!
+                        pl = fma(pl, x2, -1.98412698412698413e-04);                 // -1/7!
+                        pl = fma(pl, x2, 8.33333333333333333e-03);                  //  1/5!
+                        pl = fma(pl, x2, -1.66666666666666667e-01);                 // -1/3!
+                        S = fma(x * x2, pl, x);
+                    }
+                    double val = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
+                    if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
+                    row[kp] = val;
+                }
+            }
+        }
+    } else {
+        for (int e = tid; e < N * K; e += nthr) {
+            const int n = e / K, kp = e - n * K;
+            const int k = (kp == K - 1) ? 0 : kp + 1;
+            Imk[(long)n * ldk + kp] = imk(HARM(n), k, g, ex, mk, Nk);
+        }
+    }
+#undef HARM
+}
+
+// Parity export of the product coupling table (meemb200_imk_table): one CTA, identity row order, columns in the
+// reference's order k = 0 .. K-1.
+__global__ void __launch_bounds__(256) k_imk_dump(const void* blob, void* ws, int gi, int f, double* out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Exterior ex;
+    __shared__ int sh_row0;
+    DevView v = make_view(blob, ws);
+    const GeomDesc gd = v.geom[gi];
+    const Geom g = geom_of(v, gd);
+    const RootSet rs = v.sets[gd.root_set];
+    const int F = v.hdr->n_freq;
+    const double m0 = v.roots[rs.off + f];
+    const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+    const double* Nk = v.roots + rs.off + F + (int64_t)F * rs.K + (int64_t)f * rs.K;
+    if (threadIdx.x == 0) make_exterior(g, m0, ex);
+    __syncthreads();
+    const int N = gd.N, K = gd.K, ldk = pad8(K);
+    double* sm = reinterpret_cast<double*>(smem);
+    double* Imk = v.slots;                    // scratch: the first slot
+    cta_imk_table(g, ex, mk, Nk, N, K, ldk, nullptr, Imk, sm, 4 * K + 3 * N, &sh_row0);
+    __syncthreads();
+    for (int e = threadIdx.x; e < N * K; e += blockDim.x) {
+        const int n = e / K, k = e - n * K;
+        out[e] = Imk[(long)n * ldk + (k == 0 ? K - 1 : k - 1)];
+    }
+}
+
 __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws, int item0, int item1, int* counter, int flags) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
@@ -1001,88 +1168,8 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         const double* LA = gs + gs_base_doubles(N, R);
         const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
 #define HARM(kk) (lmode ? perm[kk] : (kk))
-        // 1. coupling table (columns permuted; rows permuted in the factorised-H form)
-        // Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
-        //   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
-        // with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
-        // sines, four divisions and a square root.  Both forms carry ~1e-13 absolute argument-rounding noise in the
-        // sines (|theta| eps, theta up to ~1e3); the exact-equality branch |m_k| == lambda is kept.  Row m = 0 and
-        // column k = 0 go through the reference-ordered imk().  (meemb200_assemble keeps imk() for every entry.)
-        const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= kGemmSmemDoubles;
-        if (fast) {
-            double* tmk = sm;               // [K] m_k (permuted)
-            double* tsk = tmk + K;          // sin(m_k L)
-            double* tck = tsk + K;          // cos(m_k L)
-            double* tnk = tck + K;          // sqrt(2 / N_k) / 2
-            double* tlm = tnk + K;          // [N] lambda_m
-            double* tsl = tlm + N;          // sin(lambda_m L)
-            double* tcl = tsl + N;          // cos(lambda_m L)
-            const double Lh = g.h - g.d[g.M - 1];
-            for (int kp = tid; kp < K; kp += nthr) {
-                const int k = (kp == K - 1) ? 0 : kp + 1;
-                const double mv = mk[k];
-                double sv, cv;
-                const double pr = mv * Lh, er = fma(mv, Lh, -pr);     // exact product = pr + er
-                sincos(pr, &sv, &cv);
-                tmk[kp] = mv; tsk[kp] = fma(er, cv, sv); tck[kp] = fma(-er, sv, cv);
-                tnk[kp] = sqrt(2.0 / Nk[k]) * 0.5;
-            }
-            for (int n = tid; n < N; n += nthr) {
-                const double lam = lambda_ni(HARM(n), g.M - 1, g);
-                double sv, cv;
-                const double pr = lam * Lh, er = fma(lam, Lh, -pr);
-                sincos(pr, &sv, &cv);
-                tlm[n] = lam; tsl[n] = fma(er, cv, sv); tcl[n] = fma(-er, sv, cv);
-            }
-            __syncthreads();
-            // row m = 0 and column k = 0 (reference-ordered forms), kept out of the main loop so that it stays uniform
-            for (int e = tid; e < N * 2; e += nthr) {                 // column k = 0 of every row; find the row of harmonic 0
-                const int kk = e >> 1;
-                if (e & 1) { if (HARM(kk) == 0) sh_row0 = kk; }
-                else Imk[(long)kk * ldk + K - 1] = imk(HARM(kk), 0, g, ex, mk, Nk);
-            }
-            __syncthreads();
-            for (int kp = tid; kp < K - 1; kp += nthr) Imk[(long)sh_row0 * ldk + kp] = imk(0, kp + 1, g, ex, mk, Nk);
-            // interior: one row per warp, lanes over the columns, branch-free except the exact-equality case.
-            //   (a + b) / sp + S / sd  over the common denominator, S = sin(sd L):  a - b away from a resonance,
-            //   x sinc(x) (Taylor, |x| = |sd L| < 1) near one, where a - b would lose digits to cancellation
-            {
-                const int lane_ = tid & 31, warp_ = tid >> 5, nwarp_ = nthr >> 5;
-                for (int n = warp_; n < N; n += nwarp_) {
-                    if (n == sh_row0) continue;
-                    const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
-                    double* row = Imk + (long)n * ldk;
-                    for (int kp = lane_; kp < K - 1; kp += 32) {
-                        const double mv = tmk[kp];
-                        const double a = tsk[kp] * cl, b = tck[kp] * sl;
-                        const double sp = mv + lam, sd = mv - lam;
-                        const double x = sd * Lh, x2 = x * x;
-                        double S = a - b;
-                        if (fabs(x) < 1.0) {
-                            double pl = -8.22063524662432972e-18;                       // -1/19!
-                            pl = fma(pl, x2, 2.81145725434552076e-15);                  //  1/17!
-                            pl = fma(pl, x2, -7.64716373181981648e-13);                 // -1/15!
-                            pl = fma(pl, x2, 1.60590438368216146e-10);                  //  1/13!
-                            pl = fma(pl, x2, -2.50521083854417188e-08);                 // -1/11!
-                            pl = fma(pl, x2, 2.75573192239858907e-06);                  //  1/9!
-                            pl = fma(pl, x2, -1.98412698412698413e-04);                 // -1/7!
-                            pl = fma(pl, x2, 8.33333333333333333e-03);                  //  1/5!
-                            pl = fma(pl, x2, -1.66666666666666667e-01);                 // -1/3!
-                            S = fma(x * x2, pl, x);
-                        }
-                        double val = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
-                        if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
-                        row[kp] = val;
-                    }
-                }
-            }
-        } else {
-            for (int e = tid; e < N * K; e += nthr) {
-                const int n = e / K, kp = e - n * K;
-                const int k = (kp == K - 1) ? 0 : kp + 1;
-                Imk[(long)n * ldk + kp] = imk(HARM(n), k, g, ex, mk, Nk);
-            }
-        }
+        // 1. coupling table (columns permuted; rows permuted in the factorised-H form): cta_imk_table
+        cta_imk_table(g, ex, mk, Nk, N, K, ldk, lmode ? perm : nullptr, Imk, sm, kGemmSmemDoubles, &sh_row0);
         for (int kp = tid; kp < K; kp += nthr) {
             const int k = (kp == K - 1) ? 0 : kp + 1;
             const cplx dg = ext_diag(k, g, ex, mk);
@@ -2163,6 +2250,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x; P->info.n_c = n_c;
+    P->info.geom_kernel = !schur ? -1 : P->use_coop ? 1 : P->band_variant >= 0 ? 2 + P->band_variant : 0;
+    P->info.reserved = 0;
     P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
@@ -2467,6 +2556,44 @@ extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws,
     k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
     k_assemble<<<1, 512, 0, s>>>(d_in, d_ws, g, f, reinterpret_cast<cplx*>(d_A), reinterpret_cast<cplx*>(d_b), reinterpret_cast<cplx*>(d_c));
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_imk_table(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f,
+                                  double* d_out, void* stream) {
+    if (!P || !d_in || !d_ws || !d_out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
+    const BlobHeader* h = P->hdr();
+    if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
+    if (h->algo != MEEMB200_ALGO_SCHUR) return fail(MEEMB200_EINVAL, "the coupling-table export needs a plan of the default algorithm");
+    const GeomDesc& gd = P->geoms[g];
+    const size_t smem = sizeof(double) * (size_t)(4 * gd.K + 3 * gd.N);
+    if (smem + 1024 > P->ctx->smem_optin || (int64_t)pad16(gd.N) * pad8(gd.K) > h->slot_doubles_freq)
+        return fail(MEEMB200_EINVAL, "system too large for the coupling-table export");
+    DeviceGuard guard(P->ctx->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    if (rc) return rc;
+    CUDA_TRY(cudaFuncSetAttribute(k_imk_dump, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_imk_dump<<<1, 256, smem, s>>>(d_in, d_ws, g, f, d_out);
+    CUDA_TRY(cudaGetLastError());
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_coefficients(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f,
+                                     const double* d_X, double* d_out, void* stream) {
+    if (!P || !d_in || !d_ws || !d_X || !d_out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
+    const BlobHeader* h = P->hdr();
+    if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
+    DeviceGuard guard(P->ctx->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    if (rc) return rc;
+    k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
+    CUDA_TRY(cudaGetLastError());
+    k_reduce<<<1, 128, 0, s>>>(d_in, d_ws, g, f, reinterpret_cast<const cplx*>(d_X), d_out);
     CUDA_TRY(cudaGetLastError());
     return MEEMB200_OK;
 }

@@ -58,3 +58,107 @@ def gather_padded(local, group=None):
     out = torch.empty(mx * world, dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(out, buf, group=group)
     return [out[r * mx:r * mx + sizes[r]] for r in range(world)]
+
+
+def geometry_cost(geo, n_freq: int) -> float:
+    """Relative device cost of one geometry with n_freq frequencies: window elimination of the geometry stage
+    (~25 N^3 per interior boundary) plus the per-frequency Schur stage (N^2 K + N K^2 + K^3 / 3)."""
+    nmk = np.asarray(geo.NMK, dtype=float)
+    N, K = nmk[-2], nmk[-1]
+    geom = float(np.sum(25.0 * nmk[:-1] ** 3))
+    return geom + n_freq * (N * N * K + N * K * K + K ** 3 / 3.0)
+
+
+class ShardedPlan:
+    """A batch spread over the ranks of a process group (one process per GPU): the product-level multi-GPU entry.
+
+    Geometry-first sharding with cost-balanced parts when there are at least as many geometries as ranks, contiguous
+    frequency chunks otherwise.  Every rank solves its shard with an ordinary ``BatchPlan``; the ONLY
+    exchange is one all_gather of the packed output buffers (NCCL over NVLink on GPUs; gloo in the CPU tests, where
+    ``plan_factory`` supplies a stand-in for the device plan).  Every rank can compute every other rank's output layout,
+    so no sizes are exchanged.
+    """
+
+    def __init__(self, geometries, freqs, group=None, plan_factory=None, want_c=False, want_x=False, **plan_kw):
+        import torch
+        import torch.distributed as dist
+        from .batch import BatchPlan, output_layout
+        self.torch, self.dist, self.group = torch, dist, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.geometries = list(geometries)
+        self.freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
+        self.want_c, self.want_x = bool(want_c), bool(want_x)
+        G, F, W = len(self.geometries), len(self.freqs), self.world
+        self.mode, _ = plan_shards(G, F, W)
+        if self.mode == "geometry":
+            costs = [geometry_cost(g, F) for g in self.geometries]
+            self.geom_parts = shard_by_cost(costs, W)
+            self.freq_parts = [(0, F)] * W
+        else:
+            self.geom_parts = [np.arange(G, dtype=np.int64)] * W
+            self.freq_parts = shard_bounds(F, W)
+        self.layouts = []
+        for r in range(W):
+            gs = [self.geometries[i] for i in self.geom_parts[r]]
+            Fr = self.freq_parts[r][1] - self.freq_parts[r][0]
+            meta = (Fr, [g.R for g in gs], [g.size for g in gs], [int(g.NMK[-1]) for g in gs])
+            self.layouts.append((meta, output_layout(*meta, self.want_c, self.want_x)))
+        self.slot_bytes = max(lay[1] for _, lay in self.layouts)
+        my_geos = [self.geometries[i] for i in self.geom_parts[self.rank]]
+        f0, f1 = self.freq_parts[self.rank]
+        factory = plan_factory or BatchPlan
+        self.local = factory(my_geos, self.freqs[f0:f1], want_c=self.want_c, want_x=self.want_x,
+                             out_bytes_min=self.slot_bytes, **plan_kw) if (len(my_geos) and f1 > f0) else None
+        dev = self.local.d_out.device if self.local is not None else torch.device("cpu")
+        self.gathered = torch.empty(self.slot_bytes * W, dtype=torch.uint8, device=dev) if W > 1 else None
+        self._empty = torch.zeros(self.slot_bytes, dtype=torch.uint8, device=dev) if self.local is None else None
+
+    def upload(self):
+        if self.local is not None:
+            self.local.upload()
+
+    def solve(self):
+        """Enqueue this rank's kernels and the gather of every rank's packed outputs (asynchronous on GPUs)."""
+        if self.local is not None:
+            self.local.solve()
+        if self.world > 1:
+            src = self.local.d_out if self.local is not None else self._empty
+            self.dist.all_gather_into_tensor(self.gathered, src, group=self.group)
+
+    def download(self):
+        """Per-geometry result dicts in the caller's geometry order, frequencies re-joined (every rank holds them all)."""
+        from .batch import split_outputs, unpack_outputs
+        if self.world == 1:
+            return self.local.split(self.local.download())
+        host = self.gathered.cpu().numpy()
+        G, F = len(self.geometries), len(self.freqs)
+        per_geom = [[None] * self.world for _ in range(G)]
+        for r in range(self.world):
+            (Fr, R, NT, K), (seg, _) = self.layouts[r]
+            if Fr == 0 or len(R) == 0:
+                continue
+            flat = unpack_outputs(host[r * self.slot_bytes:(r + 1) * self.slot_bytes], seg, len(R), Fr, self.want_c, self.want_x)
+            for gi, res in zip(self.geom_parts[r], split_outputs(flat, Fr, R, NT, K, self.want_c, self.want_x)):
+                per_geom[int(gi)][r] = res
+        out = []
+        for g in range(G):
+            parts = [x for x in per_geom[g] if x is not None]
+            if len(parts) == 1:
+                out.append(parts[0])
+            else:       # frequency chunks of one geometry, in rank order
+                merged = {k: np.concatenate([q[k] for q in parts], axis=0) for k in parts[0] if k != "c_vector"}
+                if self.want_c:
+                    merged["c_vector"] = parts[0]["c_vector"]
+                out.append(merged)
+        return out
+
+    def run(self):
+        self.upload()
+        self.solve()
+        return self.download()
+
+
+def solve_batch_distributed(geometries, freqs, group=None, **kw):
+    """`solve_batch` over every GPU of the process group: shard, solve, one all_gather, results on every rank."""
+    return ShardedPlan(geometries, freqs, group=group, **kw).run()

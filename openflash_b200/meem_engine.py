@@ -121,42 +121,19 @@ class MEEMEngine:
 
     def compute_hydrodynamic_coefficients(self, problem, X, m0, modes_to_calculate=None, rho=None):
         """Reduce a solution X to one dict per mode j (meem_engine.py:326-393).  The c vectors and the
-        particular-solution integrals come from the device; the dot product runs on the device too."""
-        import torch
+        particular-solution integrals, the dot products and the phase / force formulas all run in the device kernel
+        k_reduce (meemb200_coefficients)."""
         rho = RHO_DEFAULT if rho is None else rho
         bodies = problem.geometry.body_arrangement.bodies
         if modes_to_calculate is None:
             modes_to_calculate = np.arange(len(bodies))
         modes_to_calculate = [int(m) for m in modes_to_calculate]
         geo = flatten_problem(problem, modes=modes_to_calculate)
-        plan = BatchPlan([geo], [m0], freq_kind=FREQ_M0, device=self.device)
-        _, _, c, phi = plan.assemble(0, 0)
-        K = int(geo.NMK[-1])
-        h = geo.h
-        dev = plan.device
-        Xd = torch.from_numpy(np.ascontiguousarray(np.asarray(X, dtype=np.complex128)[:-K])).to(dev)
-        cd = torch.from_numpy(np.ascontiguousarray(c)).to(dev)
-        dots = (cd @ Xd).cpu().numpy()
-        if np.isinf(m0):
-            phase = -(np.pi / 2)
-            om = np.inf
-        else:
-            x = np.array([m0 * geo.a[-1]])
-            j0, y0 = _batch.device_bessel(4, x, self.device)[0], _batch.device_bessel(5, x, self.device)[0]
-            phase = -(np.pi / 2) + np.angle(X[-K]) - np.arctan2(y0, j0)
-            om = np.sqrt(m0 * np.tanh(m0 * h) * G_CONST)
-        out = []
-        for j, mode in enumerate(modes_to_calculate):
-            coef = 2 * np.pi * (dots[j] + phi[j])
-            re = coef.real * rho
-            im = 0 if np.isinf(m0) else coef.imag * om * rho
-            with np.errstate(all="ignore"):
-                T = np.tanh(m0 * h)
-                const = T + m0 * h * (1 - T ** 2)
-                force = np.sqrt(np.float64((2 * const * RHO_DEFAULT * (G_CONST ** 2) * im) / (om * m0)))
-            out.append({"mode": mode, "real": re, "imag": im, "excitation_phase": phase,
-                        "excitation_force": force, "c_vector": c[j]})
-        return out
+        plan = BatchPlan([geo], [m0], freq_kind=FREQ_M0, device=self.device, rho=rho)
+        vals = plan.coefficients(X, 0, 0)               # k_reduce: [mode j][real, imag, phase, force]
+        _, _, c, _ = plan.assemble(0, 0)
+        return [{"mode": mode, "real": vals[j, 0], "imag": (0 if np.isinf(m0) else vals[j, 1]), "excitation_phase": vals[j, 2],
+                 "excitation_force": vals[j, 3], "c_vector": c[j]} for j, mode in enumerate(modes_to_calculate)]
 
     # ------------------------------------------------------------------ fields (SURVEY §8f rank 1)
     @staticmethod
@@ -230,9 +207,11 @@ class MEEMEngine:
         """Frequency x mode sweep of one problem (meem_engine.py:555-690) in ONE device batch."""
         return self.run_batch([self.problem_list[problem_index]])[0]
 
-    def run_batch(self, problems: Sequence[MEEMProblem], want_potentials: bool = True) -> List[Results]:
+    def run_batch(self, problems: Sequence[MEEMProblem], want_potentials: bool = True, group=None) -> List[Results]:
         """Many problems at once.  Problems sharing a frequency grid go into one device batch
-        (geometry x frequency x mode); different grids are grouped."""
+        (geometry x frequency x mode); different grids are grouped.  With ``group`` (a torch.distributed process
+        group, one process per GPU) every batch is sharded over the group's GPUs (openflash_b200.distributed.ShardedPlan)
+        and every rank returns the complete results."""
         problems = list(problems)
         groups: Dict[bytes, List[int]] = {}
         for idx, prob in enumerate(problems):
@@ -248,16 +227,20 @@ class MEEMEngine:
                 if len(modes) == 0:
                     raise ValueError("problem has no heaving body: nothing to radiate")
                 flats.append(flatten_problem(prob, modes=list(modes)))
-            plan = BatchPlan(flats, omegas, want_x=want_potentials, device=self.device, algo=self.algo)
-            out = plan.run()
+            if group is not None:
+                from .distributed import ShardedPlan
+                out = ShardedPlan(flats, omegas, group=group, want_x=want_potentials, want_c=True, device=self.device,
+                                  algo=self.algo).run()
+            else:
+                out = BatchPlan(flats, omegas, want_x=want_potentials, want_c=True, device=self.device, algo=self.algo).run()
             for i, geo, r in zip(idxs, flats, out):
                 prob = problems[i]
                 res = Results(prob)
                 F, R = len(omegas), geo.R
                 p = geo.size - int(geo.NMK[-1])
-                # the c vector reported per (frequency, mode) is that of mode j = i (eng.py:646-652)
-                _, _, c, _ = BatchPlan([geo], [1.0], freq_kind=FREQ_M0, device=self.device).assemble(0, 0)
-                cmat = np.broadcast_to(c[None, :, :], (F, R, p)).copy()
+                # the c vector reported per (frequency, mode) is that of mode j = i (eng.py:646-652); it is frequency
+                # independent and comes out of the same batch call (MeemOutputs.c_vector)
+                cmat = np.broadcast_to(r["c_vector"].astype(complex)[None, :, :], (F, R, p)).copy()
                 bad = r["status"] != 0
                 cmat[bad] = np.nan + 0j
                 res.store_hydrodynamic_coefficients(frequencies=prob.frequencies, added_mass_matrix=r["added_mass"],

@@ -83,6 +83,8 @@ def gen_single():
                 out[key + "/imag"] = np.array([r["imag"] for r in res])
                 out[key + "/phase"] = np.array([r["excitation_phase"] for r in res])
                 out[key + "/force"] = np.array([r["excitation_force"] for r in res])
+                if mi == 0:          # the c vectors (one per mode j) do not depend on m0
+                    out[key + "/c"] = np.array([r["c_vector"] for r in res])
     out["__meta__"] = np.array(json.dumps(meta))
     np.savez_compressed(os.path.join(HERE, "ref_single.npz"), **out)
     print("ref_single.npz:", len(out), "arrays")
@@ -125,6 +127,7 @@ def gen_sweeps():
             out[f"{name}/{var}"] = np.asarray(ds[var].values)
         pot = np.asarray(ds["potentials_real"].values) + 1j * np.asarray(ds["potentials_imag"].values)
         out[f"{name}/potentials"] = pot
+        out[f"{name}/c_vector"] = np.asarray(ds["c_vector"].values)        # (frequency, mode_i, p) complex, eng.py:646-652
         out[f"{name}/m0"] = np.array([of.wavenumber(w, c["h"]) for w in s["omegas"]])
         meta[name] = dict(h=c["h"], a=list(map(float, c["a"])), d=list(map(float, c["d"])), NMK=list(c["NMK"]),
                           body_map=list(c["body_map"]), omegas=list(map(float, s["omegas"])), modes=list(s["modes"]))

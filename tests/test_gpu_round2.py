@@ -254,3 +254,170 @@ def test_solve_host_single_mode_null_outputs_and_einval(ofb):
     rc, _ = _raw_solve_host(ofb, h, a, d, NMK, [[1, 1]], [0.0, 1.0], False)
     assert rc == -1 and b"positive" in lib.meemb200_last_error()
     assert lib.meemb200_solve_host(None, None, None) == -1
+
+
+# ------------------------------------------------------------------------------------------------ c vector, reduction
+@pytest.mark.parametrize("name", sorted(META2))
+def test_c_vector_output_values_vs_reference(ofb, name):
+    """MeemOutputs.c_vector (one [R][p] block per geometry out of the batch call) against the c_vector variable of the
+    untouched reference's run_and_store_results (frequency, mode, p), <= 1e-12."""
+    key = f"{name}/c_vector"
+    if key not in Z2:
+        pytest.skip("fixture without c_vector")
+    s = META2[name]
+    geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
+    res = ofb.BatchPlan([geo, geo], s["omegas"], want_c=True).run()
+    cref = Z2[key]
+    assert np.all(cref.imag == 0)
+    for r in res:
+        assert r["c_vector"].shape == cref.shape[1:]
+        for f in range(cref.shape[0]):
+            assert relerr(r["c_vector"], cref[f].real) <= 1e-12
+
+
+def test_engine_dataset_c_vector_and_assemble_c_values(ofb):
+    """MEEMEngine.run_and_store_results -> dataset['c_vector'] values (not only shapes), assemble_c_multi values, and
+    compute_hydrodynamic_coefficients for a given X through the device reduction (k_reduce)."""
+    name = "tutorial_2body"
+    s = META2[name]
+    geo = ofb.BasicRegionGeometry.from_vectors(a=np.asarray(s["a"]), d=np.asarray(s["d"]), h=s["h"], NMK=list(s["NMK"]),
+                                               body_map=list(s["body_map"]), heaving_map=[False] * (max(s["body_map"]) + 1))
+    prob = ofb.MEEMProblem(geo)
+    for bi, body in enumerate(prob.geometry.body_arrangement.bodies):
+        body.heaving = bi in s["modes"]
+    prob.set_frequencies(np.asarray(s["omegas"], float))
+    eng = ofb.MEEMEngine([prob])
+    ds = eng.run_and_store_results(0).dataset
+    cref = Z2[f"{name}/c_vector"]
+    got = np.asarray(ds["c_vector"].values)
+    assert got.shape == cref.shape and relerr(got.real, cref.real) <= 1e-12 and np.all(got.imag == 0)
+    # assemble_c_multi for region flags [1, 0]: the c vector of mode 0
+    c0 = eng.assemble_c_multi(prob, [1, 0])
+    assert relerr(c0.real, cref[0, 0].real) <= 1e-12
+    # reduction of the reference's own X (golden single-solve fixtures)
+    c = META1["small_bicylinder_2body"]
+    geo1 = ofb.BasicRegionGeometry.from_vectors(a=np.asarray(c["a"]), d=np.asarray(c["d"]), h=c["h"], NMK=list(c["NMK"]),
+                                                body_map=list(c["body_map"]), heaving_map=[True, False])
+    p1 = ofb.MEEMProblem(geo1)
+    e1 = ofb.MEEMEngine([p1])
+    for mi, m0 in enumerate(c["m0"]):
+        key = f"small_bicylinder_2body/b0/m{mi}"
+        out = e1.compute_hydrodynamic_coefficients(p1, Z1[key + "/X"], m0)
+        assert relerr([o["real"] for o in out], Z1[key + "/real"]) <= 1e-11
+        assert relerr([o["imag"] for o in out], Z1[key + "/imag"]) <= 1e-11
+        assert phase_err([o["excitation_phase"] for o in out], Z1[key + "/phase"]) <= 1e-11
+        fr = Z1[key + "/force"]
+        okf = np.isfinite(fr)
+        assert relerr(np.array([o["excitation_force"] for o in out])[okf], fr[okf]) <= 1e-11
+        if key + "/c" in Z1:
+            assert relerr(np.array([o["c_vector"] for o in out]).real, Z1[key + "/c"].real) <= 1e-12
+
+
+def test_run_batch_many_geometries_is_one_plan(ofb):
+    """run_batch over 300 problems: c_vector comes out of the batch call (no per-geometry plan), values equal to the
+    single-problem run, and the whole call stays within a small multiple of the bare BatchPlan.run()."""
+    import time
+    import bench
+    gs = bench.c4_geometries(300)
+    om = np.linspace(0.3, 2.5, 8)
+    probs = []
+    for g in gs:
+        geo = ofb.BasicRegionGeometry.from_vectors(a=np.asarray(g["a"]), d=np.asarray(g["d"]), h=g["h"], NMK=list(g["NMK"]),
+                                                   body_map=list(g["body_map"]), heaving_map=[True])
+        p = ofb.MEEMProblem(geo)
+        p.set_frequencies(om)
+        probs.append(p)
+    eng = ofb.MEEMEngine(probs)
+    eng.run_batch(probs[:4], want_potentials=False)            # warm-up (context, kernels)
+    t0 = time.perf_counter()
+    out = eng.run_batch(probs, want_potentials=False)
+    t_engine = time.perf_counter() - t0
+    flats = [ofb.flatten_problem(p, modes=list(p.modes)) for p in probs]
+    t0 = time.perf_counter()
+    raw = ofb.BatchPlan(flats, om, want_c=True).run()
+    t_plan = time.perf_counter() - t0
+    for r, q in zip(out, raw):
+        assert np.array_equal(np.asarray(r.dataset["added_mass"].values), q["added_mass"])
+        assert np.array_equal(np.asarray(r.dataset["c_vector"].values)[0].real, q["c_vector"])
+    assert t_engine < 4.0 * t_plan + 0.5, (t_engine, t_plan)
+
+
+# ------------------------------------------------------------------------------------------------ waves, depths
+def test_multi_wave_frequency_stage_is_bit_identical(ofb, monkeypatch):
+    """The frequency stage in 3+ waves (per-wave counters, item offsets, reuse of the system buffers) reproduces the
+    single-wave run bit for bit - CTA-per-system kernels (small_tricylinder_n20, 3 bodies) and the one-warp kernel."""
+    cases = [(20.0, [5.0, 10.0, 15.0], [15.0, 10.0, 5.0], [20, 20, 20, 20], [0, 1, 2], [0, 1, 2], 40),
+             (1.001, [0.125, 0.25], [0.25, 0.125], [10, 10, 10], [0, 0], [0], 300)]
+    for h, a, d, NMK, bm, modes, F in cases:
+        geo = ofb.FlatGeometry.from_body_map(h, a, d, NMK, bm, modes)
+        om = np.linspace(0.2, 3.0, F)
+        one = ofb.solve_batch([geo, geo, geo], om)
+        monkeypatch.setenv("MEEMB200_WAVE_ITEMS", str(F))          # 3 geometries x F systems -> 3 waves
+        many = ofb.solve_batch([geo, geo, geo], om)
+        monkeypatch.delenv("MEEMB200_WAVE_ITEMS")
+        for r1, r2 in zip(one, many):
+            assert np.all(r1["status"] == 0) and np.all(r2["status"] == 0)
+            for v in ("added_mass", "damping", "excitation_force", "excitation_phase"):
+                assert np.array_equal(r1[v], r2[v]), v
+
+
+def test_heterogeneous_depths_batch(ofb):
+    """Every geometry its own water depth: one root set per geometry (hashed by (h, K) in the planner, k_mk folds the
+    set index), results equal to solving each geometry alone and to the oracle for a few."""
+    rng = np.random.default_rng(11)
+    hs = rng.uniform(5.0, 80.0, 600)
+    om = np.array([0.4, 1.2, 2.4])
+    geos = [ofb.FlatGeometry(float(h), [1.0, 2.5], [0.3 * h, 0.1 * h], [8, 8, 8]) for h in hs]
+    res = ofb.solve_batch(geos, om)
+    for i in (0, 299, 599):
+        alone = ofb.solve_batch([geos[i]], om)[0]
+        for v in ("added_mass", "damping", "excitation_force", "excitation_phase", "m0"):
+            assert np.array_equal(res[i][v], alone[v]), v
+        ref = mo.run_sweep(mo.FlatGeometry(float(hs[i]), [1.0, 2.5], [0.3 * hs[i], 0.1 * hs[i]], [8, 8, 8]), om, [0, 0], [0])
+        _check(res[i], ref)
+
+
+def test_plan_argument_errors(ofb):
+    """n_geom * n_freq beyond int32 and omega = inf in set_frequencies are refused with EINVAL (ValueError)."""
+    geo = ofb.FlatGeometry(1.001, [0.5, 1.0], [0.5, 0.25], [4, 4, 4])
+    plan = ofb.BatchPlan([geo], [1.0, 2.0])
+    with pytest.raises(ValueError, match="finite"):
+        plan.set_frequencies([1.0, np.inf])
+    with pytest.raises(ValueError, match="positive"):
+        plan.set_frequencies([1.0, -2.0])
+
+
+def test_product_imk_table_entries(ofb):
+    """Entry-level check of the coupling table the frequency stage really uses (angle-addition form + sinc series +
+    exact-equality branch) against the oracle's reference-ordered I_mk_table (multi_equations.py:96-124): bicylinder with
+    near-resonant (m_k - lambda) L < 1 columns, the asymptotic m0 h >= 14 branch, and a geometry built so that
+    |m_k| == lambda exactly for one (m, k) pair."""
+    cases = [(1.001, [0.5, 1.0], [0.5, 0.25], [30, 30, 30], [0.5, 2.0, 12.0]),
+             (20.0, [5.0, 10.0, 15.0], [15.0, 10.0, 5.0], [50, 50, 50, 50], [0.3, 2.7, 3.0]),
+             (50.0, [2.0, 5.0], [20.0, 3.0], [16, 16, 16], [0.3, 1.4, 2.5])]
+    for h, a, d, NMK, oms in cases:
+        geo = ofb.FlatGeometry(h, a, d, NMK)
+        plan = ofb.BatchPlan([geo], oms)
+        og = mo.FlatGeometry(h, a, d, NMK)
+        near = 0
+        for f, w in enumerate(oms):
+            m0 = mo.wavenumber(w, h)
+            mk = mo.m_k_array(NMK[-1], m0, h)
+            Nk = mo.N_k_array(m0, h, mk)
+            ref = mo.I_mk_table(og, m0, mk, Nk)
+            got = plan.imk_table(0, f)
+            assert got.shape == ref.shape
+            assert np.max(np.abs(got - ref)) <= 1e-13 * np.max(np.abs(ref))
+            lam = np.arange(NMK[-2]) * np.pi / (h - d[-1])
+            near += int(np.sum(np.abs(mk[None, 1:] - lam[1:, None]) * (h - d[-1]) < 1.0))
+        assert near > 0          # the sinc-series branch was exercised
+    # exact equality |m_k| == lambda: with m0 = inf, m_k = (k - 1/2) pi / h; choose d so that lambda_n = n pi / (h - d) hits it:
+    # h = 3, d = 1 -> lambda_1 = pi / 2 = m_2 ... (k - 1/2) / 3 = n / 2 -> k = 2, n = 1
+    geo = ofb.FlatGeometry(3.0, [1.0], [1.0], [6, 6])
+    plan = ofb.BatchPlan([geo], [np.inf], freq_kind=ofb.FREQ_M0)
+    mk = mo.m_k_array(6, np.inf, 3.0)
+    Nk = mo.N_k_array(np.inf, 3.0, mk)
+    ref = mo.I_mk_table(mo.FlatGeometry(3.0, [1.0], [1.0], [6, 6]), np.inf, mk, Nk)
+    got = plan.imk_table(0, 0)
+    assert abs(mk[2]) == 1 * np.pi / 2.0                       # the branch is really hit
+    assert np.max(np.abs(got - ref)) <= 1e-13 * np.max(np.abs(ref))
