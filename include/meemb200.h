@@ -91,7 +91,8 @@ typedef struct MeemPlanInfo {
     int32_t geom_kernel;      /* geometry-stage kernel the plan chose: 0 dense LU per CTA (k_geom), 1 grid-cooperative dense LU
                                * (k_geom_coop), 2/3/4 window elimination (k_geom_band: small shared-memory window / shared-memory
                                * window / global-slot window), -1 none (ALGO_DENSE) */
-    int32_t reserved;
+    int32_t freq_kernel;      /* frequency-stage kernels: 0 k_freq_gemm + k_freq_solve (Cholesky), 1 k_freq_small (one warp per system),
+                               * 2 k_freq_lu (pivoted LU), 3 k_dense (ALGO_DENSE) */
 } MeemPlanInfo;
 
 /* Device output pointers (caller-owned).  Layouts are the reference's (meem_engine.py:573-580):
@@ -137,8 +138,10 @@ int meemb200_plan_set_freq(meemb200_plan* plan, const double* freq);
 int meemb200_solve(meemb200_plan* plan, const void* d_input, void* d_workspace, size_t workspace_bytes,
                    const MeemOutputs* out, void* stream);
 
-/* Host-buffer convenience: allocates device memory (stream-ordered), uploads, solves, downloads
- * into HOST pointers of `out`, synchronises.  This is the end-to-end call with host buffers. */
+/* Host-buffer call (what the reference-side stub of INTEGRATION.md binds): uploads the packed inputs, solves, downloads
+ * into the HOST pointers of `out` (any of exc_force / exc_phase / m0 / x / c_vector may be NULL), synchronises.
+ * The one entry point that owns device memory: the first call allocates inputs + workspace + outputs with cudaMalloc
+ * and the plan keeps the allocation for later calls (released by meemb200_plan_destroy). */
 int meemb200_solve_host(meemb200_plan* plan, const MeemOutputs* host_out, void* stream);
 
 /* Parity / debugging exports mirroring the reference's intermediate API (device pointers).

@@ -33,7 +33,7 @@ class MeemPlanInfo(C.Structure):
         ("input_bytes", C.c_size_t), ("workspace_bytes", C.c_size_t),
         ("n_rr", C.c_int64), ("n_r", C.c_int64), ("n_sys", C.c_int64), ("n_x", C.c_int64),
         ("n_launches", C.c_int64), ("flops", C.c_double), ("n_c", C.c_int64),
-        ("geom_kernel", C.c_int32), ("reserved", C.c_int32),
+        ("geom_kernel", C.c_int32), ("freq_kernel", C.c_int32),
     ]
 
 

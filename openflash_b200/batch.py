@@ -365,6 +365,10 @@ class BatchPlan:
     def geom_kernel(self):
         return self.GEOM_KERNELS[int(self.info.geom_kernel)]
 
+    @property
+    def freq_kernel(self):
+        return ("k_freq_gemm+k_freq_solve", "k_freq_small", "k_freq_lu", "k_dense")[int(self.info.freq_kernel)]
+
     def coefficients(self, X, g=0, f=0):
         """compute_hydrodynamic_coefficients for a caller-supplied solution X ([NT] complex) of system (g, f): array
         [R, 4] = real, imag, excitation_phase, excitation_force per mode j of the plan (meem_engine.py:326-393)."""

@@ -1973,6 +1973,8 @@ struct meemb200_plan {
     int64_t max_FK;
     cudaEvent_t ev[6];      // 0 start, 1 after roots, 2 after geometry, 3 after last k_freq_gemm, 4 after last k_freq_solve, 5 end
     bool ev_ok;
+    char* host_call_base;   // device allocation of meemb200_solve_host (the one call that owns device memory), kept for the next call
+    size_t host_call_bytes;
 };
 
 extern "C" int meemb200_version(void) { return 200; }
@@ -2030,6 +2032,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     meemb200_plan* P = new meemb200_plan;
     P->ctx = ctx;
     P->ev_ok = false;
+    P->host_call_base = nullptr; P->host_call_bytes = 0;
     P->geoms.resize(G);
     std::vector<RootSet> sets;
     std::map<std::pair<uint64_t, int>, int> set_index;
@@ -2251,7 +2254,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x; P->info.n_c = n_c;
     P->info.geom_kernel = !schur ? -1 : P->use_coop ? 1 : P->band_variant >= 0 ? 2 + P->band_variant : 0;
-    P->info.reserved = 0;
+    P->info.freq_kernel = !schur ? 3 : b->algo == MEEMB200_ALGO_SCHUR_LU ? 2 : P->use_small ? 1 : 0;
     P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
@@ -2261,6 +2264,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
 
 extern "C" int meemb200_plan_destroy(meemb200_plan* p) {
     if (p && p->ev_ok) for (auto& e : p->ev) cudaEventDestroy(e);
+    if (p && p->host_call_base) { DeviceGuard guard(p->ctx->device); cudaFree(p->host_call_base); }
     delete p;
     return MEEMB200_OK;
 }
@@ -2510,8 +2514,12 @@ extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void
     auto take = [&](size_t n) { size_t o = off; off = align_up(off + n, 256); return o; };
     const size_t o_in = take(I.input_bytes), o_ws = take(I.workspace_bytes), o_am = take(b_rr), o_dp = take(b_rr), o_f = take(b_r),
                  o_p = take(b_r), o_m0 = take(b_m0), o_st = take(b_st), o_x = take(b_x), o_c = take(b_c);
-    char* base = nullptr;
-    CUDA_TRY(cudaMallocAsync(reinterpret_cast<void**>(&base), off, s));
+    if (P->host_call_bytes < off) {          // first call (or a larger request): the allocation stays with the plan
+        if (P->host_call_base) { CUDA_TRY(cudaFree(P->host_call_base)); P->host_call_base = nullptr; P->host_call_bytes = 0; }
+        CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&P->host_call_base), off));
+        P->host_call_bytes = off;
+    }
+    char* base = P->host_call_base;
     MeemOutputs d;
     d.added_mass = reinterpret_cast<double*>(base + o_am); d.damping = reinterpret_cast<double*>(base + o_dp);
     d.exc_force = reinterpret_cast<double*>(base + o_f); d.exc_phase = reinterpret_cast<double*>(base + o_p);
@@ -2537,7 +2545,6 @@ extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void
         back(ho->x, d.x, I.n_x ? b_x : 0);
         back(ho->c_vector, d.c_vector, b_c);
     }
-    cudaFreeAsync(base, s);
     e = cudaStreamSynchronize(s);
     if (!rc && e != cudaSuccess) rc = fail(MEEMB200_ECUDA, std::string("solve_host: ") + cudaGetErrorString(e));
     return rc;

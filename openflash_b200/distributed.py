@@ -112,6 +112,7 @@ class ShardedPlan:
                              out_bytes_min=self.slot_bytes, **plan_kw) if (len(my_geos) and f1 > f0) else None
         dev = self.local.d_out.device if self.local is not None else torch.device("cpu")
         self.gathered = torch.empty(self.slot_bytes * W, dtype=torch.uint8, device=dev) if W > 1 else None
+        self.h_gathered = (torch.empty(self.slot_bytes * W, dtype=torch.uint8, pin_memory=dev.type == "cuda") if W > 1 else None)
         self._empty = torch.zeros(self.slot_bytes, dtype=torch.uint8, device=dev) if self.local is None else None
 
     def upload(self):
@@ -126,12 +127,24 @@ class ShardedPlan:
             src = self.local.d_out if self.local is not None else self._empty
             self.dist.all_gather_into_tensor(self.gathered, src, group=self.group)
 
+    def download_packed(self):
+        """ONE device->host copy of every rank's packed outputs into pinned memory; returns the uint8 host buffer
+        (rank r's slot at r * slot_bytes, laid out by ``layouts[r]``).  `download` turns it into per-geometry dicts."""
+        if self.world == 1:
+            self.local.h_out.copy_(self.local.d_out, non_blocking=True)
+            self.torch.cuda.current_stream(self.local.device).synchronize()
+            return self.local.h_out.numpy()
+        self.h_gathered.copy_(self.gathered, non_blocking=True)
+        if self.gathered.is_cuda:
+            self.torch.cuda.current_stream(self.gathered.device).synchronize()
+        return self.h_gathered.numpy()
+
     def download(self):
         """Per-geometry result dicts in the caller's geometry order, frequencies re-joined (every rank holds them all)."""
         from .batch import split_outputs, unpack_outputs
         if self.world == 1:
             return self.local.split(self.local.download())
-        host = self.gathered.cpu().numpy()
+        host = self.download_packed()
         G, F = len(self.geometries), len(self.freqs)
         per_geom = [[None] * self.world for _ in range(G)]
         for r in range(self.world):
