@@ -159,7 +159,14 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
                 const double* cur = sm + (c % kGemmStages) * kGemmStageDoubles;
                 const double* As = cur + rb0 * 8 + lr;
                 const double* Bs = cur + kGemmKC * kGemmLdA + cb0 * 8 + lr;
-                switch (shape) {
+                // triangular operand: contraction rows k of this chunk only reach output rows m <= k + tri, i.e. the first
+                // `na` 8-row blocks of the warp tile (8-row granularity at no cost: the block count is a template argument)
+                int shape_c = shape;
+                if (tri >= 0 && shape >= 0) {
+                    const int na = min(nri, ((c + 1) * kGemmKC + tri - (m0 + rb0 * 8) + 7) >> 3);
+                    shape_c = na > 0 ? (na - 1) * 4 + (nci - 1) : -1;
+                }
+                switch (shape_c) {
 #define MEEM_GEMM_CASE(NI, NJ) case (NI - 1) * 4 + (NJ - 1): gemm_chunk<NI, NJ>(As, Bs, lc, acc); break;
                     MEEM_GEMM_CASE(1, 1) MEEM_GEMM_CASE(1, 2) MEEM_GEMM_CASE(1, 3) MEEM_GEMM_CASE(1, 4)
                     MEEM_GEMM_CASE(2, 1) MEEM_GEMM_CASE(2, 2) MEEM_GEMM_CASE(2, 3) MEEM_GEMM_CASE(2, 4)

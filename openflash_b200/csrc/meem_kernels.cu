@@ -1000,7 +1000,7 @@ enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, 
 // Coupling table I_mk of one (geometry, frequency) system as the frequency stage consumes it: Imk[row][kp] with
 // column kp = exterior mode kp + 1 (the propagating mode k = 0 is carried LAST, kp = K - 1) and row kk = harmonic
 // perm[kk] of the last interior region (perm == nullptr: identity).  All threads of the CTA must call; sm needs
-// 4K + 3N doubles for the angle-addition form (else every entry goes through the reference-ordered imk()).
+// 6K + 3N doubles for the angle-addition form (else every entry goes through the reference-ordered imk()).
 // Interior entries (m >= 1, k >= 1) use the angle-addition form of me.py:119-124:
 //   sin((m_k +- lambda) L) = sin(m_k L) cos(lambda L) +- cos(m_k L) sin(lambda L)
 // with the 2K + 2N sines/cosines tabulated once per system, so an entry costs two divisions instead of two
@@ -1011,13 +1011,15 @@ __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* m
                               const int* perm, double* Imk, double* sm, int sm_doubles, int* sh_row0) {
     const int tid = threadIdx.x, nthr = blockDim.x;
 #define HARM(kk) (perm ? perm[kk] : (kk))
-    const bool fast = !ex.inf_m0 && (4 * K + 3 * N) <= sm_doubles;
+    const bool fast = !ex.inf_m0 && (6 * K + 3 * N) <= sm_doubles;
     if (fast) {
         double* tmk = sm;               // [K] m_k (permuted)
         double* tsk = tmk + K;          // sin(m_k L)
         double* tck = tsk + K;          // cos(m_k L)
         double* tnk = tck + K;          // sqrt(2 / N_k) / 2
-        double* tlm = tnk + K;          // [N] lambda_m
+        double* tpk = tnk + K;          // 2 tnk m_k sin(m_k L)
+        double* tqk = tpk + K;          // 2 tnk cos(m_k L)
+        double* tlm = tqk + K;          // [N] lambda_m
         double* tsl = tlm + N;          // sin(lambda_m L)
         double* tcl = tsl + N;          // cos(lambda_m L)
         const double Lh = g.h - g.d[g.M - 1];
@@ -1027,8 +1029,9 @@ __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* m
             double sv, cv;
             const double pr = mv * Lh, er = fma(mv, Lh, -pr);     // exact product = pr + er
             sincos(pr, &sv, &cv);
-            tmk[kp] = mv; tsk[kp] = fma(er, cv, sv); tck[kp] = fma(-er, sv, cv);
-            tnk[kp] = sqrt(2.0 / Nk[k]) * 0.5;
+            const double sk = fma(er, cv, sv), ck = fma(-er, sv, cv), nk2 = sqrt(2.0 / Nk[k]) * 0.5;
+            tmk[kp] = mv; tsk[kp] = sk; tck[kp] = ck; tnk[kp] = nk2;
+            tpk[kp] = 2.0 * nk2 * mv * sk; tqk[kp] = 2.0 * nk2 * ck;
         }
         for (int n = tid; n < N; n += nthr) {
             const double lam = lambda_ni(HARM(n), g.M - 1, g);
@@ -1046,22 +1049,26 @@ __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* m
         }
         __syncthreads();
         for (int kp = tid; kp < K - 1; kp += nthr) Imk[(long)(*sh_row0) * ldk + kp] = imk(0, kp + 1, g, ex, mk, Nk);
-        // interior: one row per warp, lanes over the columns, branch-free except the exact-equality case.
-        //   (a + b) / sp + S / sd  over the common denominator, S = sin(sd L):  a - b away from a resonance,
-        //   x sinc(x) (Taylor, |x| = |sd L| < 1) near one, where a - b would lose digits to cancellation
+        // interior: one row per warp, lanes over the columns.  With a = sin(m_k L) cos(lam L), b = cos(m_k L) sin(lam L),
+        // sp = m_k + lam, sd = m_k - lam the entry is  nk [(a + b) / sp + sin(sd L) / sd].  Away from a resonance
+        // (|sd L| >= 1) sin(sd L) = a - b and the sum over the common denominator collapses to the rank-2 form
+        //   nk (2 m_k a - 2 lam b) / (sp sd) = (P_k cos(lam L) - Q_k lam sin(lam L)) / (sp sd)
+        // with P_k, Q_k tabulated per column: 8 FP64 instructions and one division per entry.  Near a resonance a - b
+        // would lose digits to cancellation: sin(x) = x sinc(x) by its Taylor series (|x| < 1) in the two-term form.
         {
             const int lane_ = tid & 31, warp_ = tid >> 5, nwarp_ = nthr >> 5;
             for (int n = warp_; n < N; n += nwarp_) {
                 if (n == (*sh_row0)) continue;
                 const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
+                const double lsl = lam * sl;
                 double* row = Imk + (long)n * ldk;
                 for (int kp = lane_; kp < K - 1; kp += 32) {
                     const double mv = tmk[kp];
-                    const double a = tsk[kp] * cl, b = tck[kp] * sl;
                     const double sp = mv + lam, sd = mv - lam;
-                    const double x = sd * Lh, x2 = x * x;
-                    double S = a - b;
+                    const double x = sd * Lh;
+                    double val = fma(tpk[kp], cl, -(tqk[kp] * lsl)) / (sp * sd);
                     if (fabs(x) < 1.0) {
+                        const double x2 = x * x;
                         double pl = -8.22063524662432972e-18;                       // -1/19!
                         pl = fma(pl, x2, 2.81145725434552076e-15);                  //  1/17!
                         pl = fma(pl, x2, -7.64716373181981648e-13);                 // -1/15!
@@ -1071,10 +1078,11 @@ __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* m
                         pl = fma(pl, x2, -1.98412698412698413e-04);                 // -1/7!
                         pl = fma(pl, x2, 8.33333333333333333e-03);                  //  1/5!
                         pl = fma(pl, x2, -1.66666666666666667e-01);                 // -1/3!
-                        S = fma(x * x2, pl, x);
+                        const double S = fma(x * x2, pl, x);
+                        const double a = tsk[kp] * cl, b = tck[kp] * sl;
+                        val = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
+                        if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
                     }
-                    double val = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
-                    if (fabs(mv) == lam) val = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
                     row[kp] = val;
                 }
             }
@@ -1108,7 +1116,7 @@ __global__ void __launch_bounds__(256) k_imk_dump(const void* blob, void* ws, in
     const int N = gd.N, K = gd.K, ldk = pad8(K);
     double* sm = reinterpret_cast<double*>(smem);
     double* Imk = v.slots;                    // scratch: the first slot
-    cta_imk_table(g, ex, mk, Nk, N, K, ldk, nullptr, Imk, sm, 4 * K + 3 * N, &sh_row0);
+    cta_imk_table(g, ex, mk, Nk, N, K, ldk, nullptr, Imk, sm, 6 * K + 3 * N, &sh_row0);
     __syncthreads();
     for (int e = threadIdx.x; e < N * K; e += blockDim.x) {
         const int n = e / K, k = e - n * K;
@@ -2575,7 +2583,7 @@ extern "C" int meemb200_imk_table(meemb200_plan* P, const void* d_in, void* d_ws
     if (g < 0 || g >= h->n_geom || f < 0 || f >= h->n_freq) return fail(MEEMB200_EINVAL, "geometry/frequency index out of range");
     if (h->algo != MEEMB200_ALGO_SCHUR) return fail(MEEMB200_EINVAL, "the coupling-table export needs a plan of the default algorithm");
     const GeomDesc& gd = P->geoms[g];
-    const size_t smem = sizeof(double) * (size_t)(4 * gd.K + 3 * gd.N);
+    const size_t smem = sizeof(double) * (size_t)(6 * gd.K + 3 * gd.N);
     if (smem + 1024 > P->ctx->smem_optin || (int64_t)pad16(gd.N) * pad8(gd.K) > h->slot_doubles_freq)
         return fail(MEEMB200_EINVAL, "system too large for the coupling-table export");
     DeviceGuard guard(P->ctx->device);
