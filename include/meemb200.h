@@ -90,7 +90,7 @@ typedef struct MeemPlanInfo {
     int64_t n_c;              /* total elements of c_vector = sum_g R_g * p_g (frequency independent) */
     int32_t geom_kernel;      /* geometry-stage kernel the plan chose: 0 dense LU per CTA (k_geom), 1 grid-cooperative dense LU
                                * (k_geom_coop), 2/3/4 window elimination (k_geom_band: small shared-memory window / shared-memory
-                               * window / global-slot window), -1 none (ALGO_DENSE) */
+                               * window / global-slot window), 5 grid-cooperative window elimination with static pivots (k_geom_coop2), -1 none (ALGO_DENSE) */
     int32_t freq_kernel;      /* frequency-stage kernels: 0 k_freq_gemm + k_freq_solve (Cholesky), 1 k_freq_small (one warp per system),
                                * 2 k_freq_lu (pivoted LU), 3 k_dense (ALGO_DENSE) */
 } MeemPlanInfo;

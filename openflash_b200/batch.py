@@ -359,7 +359,7 @@ class BatchPlan:
         return out.cpu().numpy().reshape(N, K)
 
     GEOM_KERNELS = {-1: "none", 0: "k_geom", 1: "k_geom_coop", 2: "k_geom_band<smem,128>", 3: "k_geom_band<smem,256>",
-                    4: "k_geom_band<global,512>"}
+                    4: "k_geom_band<global,512>", 5: "k_geom_coop2"}
 
     @property
     def geom_kernel(self):

@@ -239,12 +239,12 @@ MEEM_HD void fill_tables(const Geom& g, const Layout& L, double* tab, int tid, i
 // the full matrix uses rp = L.pot_row[bd], rv = L.vel_row[bd], cshift = 0).  The last boundary writes only its
 // omega-independent potential-row diagonal blocks.
 template <class T>
-MEEM_HD void fill_A_boundary(const Geom& g, const Layout& L, const double* tab, int bd, T* A, long ld, int rp, int rv,
-                             int cshift, int tid, int nthr) {
+MEEM_HD void fill_A_boundary_at(const Geom& g, const Layout& L, const double* tab, int bd, T* A, long ld, int rp, int rv,
+                                int c1L, int c2L, int cR, int tid, int nthr) {
+    // c1L / c2L: first column of C1^bd / C2^bd, cR: first column of region bd+1 (C1^{bd+1} followed by C2^{bd+1})
     const int M = g.M;
     const int N = g.nmk[bd];
     const double* TL = tab + L.tab[bd];
-    const int c1L = L.col[bd] - cshift, c2L = c1L + N;
     const double hdL = g.h - g.d[bd];
     if (bd == M - 1) {
         for (int n = tid; n < N; n += nthr) {
@@ -255,7 +255,6 @@ MEEM_HD void fill_A_boundary(const Geom& g, const Layout& L, const double* tab, 
     }
     const int Mm = g.nmk[bd + 1];
     const double* TR = tab + L.tab[bd + 1];
-    const int cR = L.col[bd + 1] - cshift;
     const double hdR = g.h - g.d[bd + 1];
     const bool pot_left_diag = g.d[bd] > g.d[bd + 1];
     // diagonal blocks
@@ -294,6 +293,13 @@ MEEM_HD void fill_A_boundary(const Geom& g, const Layout& L, const double* tab, 
             set_real(A[(long)(rv + n) * ld + cR + Mm + m], TR[7 * Mm + m] * I);
         }
     }
+}
+
+template <class T>
+MEEM_HD void fill_A_boundary(const Geom& g, const Layout& L, const double* tab, int bd, T* A, long ld, int rp, int rv,
+                             int cshift, int tid, int nthr) {
+    const int c1 = L.col[bd] - cshift;
+    fill_A_boundary_at<T>(g, L, tab, bd, A, ld, rp, rv, c1, c1 + g.nmk[bd], L.col[bd + 1] - cshift, tid, nthr);
 }
 
 template <class T>

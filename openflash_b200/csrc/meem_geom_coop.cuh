@@ -62,7 +62,9 @@ __device__ __forceinline__ void coop_warp_argmax(unsigned long long& key, int& i
 }
 
 // Panel factorisation by one CTA (fallback for panels taller than the register-resident variant handles).  panel: shared memory, column-major [nb][prow], prow >= rows.
-__device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, double* panel, int prow,
+// srows: only the first srows rows of the panel are pivot candidates (rows beyond it - the c rows of the static-pivot
+// window kernel - are eliminated but never chosen).
+__device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, int srows, double* panel, int prow,
                                   CoopShared& S, const CoopScratch& sc) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
@@ -74,7 +76,7 @@ __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, 
     for (int j = 0; j < nb; ++j) {
         double best = -1.0;
         int bi = 0x7fffffff;
-        for (int i = j + tid; i < rows; i += nthr) {
+        for (int i = j + tid; i < srows; i += nthr) {
             const double v = fabs(panel[j * prow + i]);
             if (v > best) { best = v; bi = i; }
         }
@@ -92,7 +94,7 @@ __device__ void coop_panel_factor(double* W, long ld, int k0, int nb, int rows, 
             const int oi = S.widx[w];
             if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
         }
-        if (bi >= rows) bi = j;                                  // column of NaNs
+        if (bi >= srows) bi = j;                                 // column of NaNs
         if (tid == 0) {
             S.piv[j] = bi;
             if (!(best < INFINITY) || best < 0.0) atomicOr(&S.status, 2);
@@ -172,7 +174,7 @@ __device__ void coop_publish_block(int k0, int nb, CoopShared& S, const CoopScra
 // entries in registers; per column one warp-shuffle arg-max, two block barriers and a 2 x 16-double row exchange
 // through shared memory.  rows <= RPT * blockDim.x.
 template <int RPT>
-__device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int rows, CoopShared& S, const CoopScratch& sc) {
+__device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int rows, int srows, CoopShared& S, const CoopScratch& sc) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
     double r[RPT][kCoopNB];
@@ -194,7 +196,7 @@ __device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int ro
         for (int t = 0; t < RPT; ++t) {
             const int i = tid + t * nthr;
             const unsigned long long kv = (unsigned long long)__double_as_longlong(fabs(r[t][j]));
-            if (i >= j && i < rows && (bi == 0x7fffffff || kv > key)) { key = kv; bi = i; }
+            if (i >= j && i < srows && (bi == 0x7fffffff || kv > key)) { key = kv; bi = i; }
         }
         coop_warp_argmax(key, bi);
         if (lane == 0) { S.wkey[warp] = key; S.widx[warp] = bi; }
@@ -203,7 +205,7 @@ __device__ void coop_panel_factor_reg(double* W, long ld, int k0, int nb, int ro
         bi = (lane < nwarp) ? S.widx[lane] : 0x7fffffff;
         coop_warp_argmax(key, bi);
         const double best = __longlong_as_double((long long)key);
-        if (bi >= rows) bi = j;                                  // no candidate row
+        if (bi >= srows) bi = j;                                 // no candidate row
         if (tid == 0) {
             S.piv[j] = bi;
             if (!(best < INFINITY)) atomicOr(&S.status, 2);      // inf or NaN pivot column
@@ -321,7 +323,7 @@ __device__ void coop_panel_update(double* W, long ld, int p, int ncols, int k0, 
 #pragma unroll
         for (int ks = 0; ks < kCoopNB / 4; ++ks) bf[ks] = S.Us[ks * 4 + lc][lr];
         const int col = col0 + 2 * lc;
-        const bool pair_ok = ((col & 1) == 0);          // ld is even: 16-byte aligned pair (the pad column absorbs col + 1 == ncols)
+        const bool pair_ok = ((reinterpret_cast<size_t>(W + col) & 15) == 0);   // ld is even: 16-byte aligned pair (the pad column absorbs col + 1 == ncols)
         for (int rb0 = warp; rb0 < nrb; rb0 += 4 * nwarp) {
             double af[4][kCoopNB / 4], cv[4][2];
             bool rok[4];
@@ -436,6 +438,47 @@ __device__ void coop_backsolve(double* W, long ld, int p, int nrhs, double* ycol
         for (int i = tid; i < p; i += nthr) {
             W[(long)i * ld + colA] = y0[i];
             if (two) W[(long)i * ld + colA + 1] = y1[i];
+        }
+    }
+}
+
+// Static-pivot elimination of a block of Nb unknowns whose pivot rows form a DIAGONAL block (the C1 columns of a region
+// against the potential rows of its outer boundary, k_geom_coop2): for every row r < nrows and column c < ncols
+//   W[r][c] -= sum_k (W[r][c1L + k] * dinv[k]) * W[potr0 + k][c]
+// as a grid-wide DMMA product, 8 x 32 tiles per warp, operand fragments straight from L2 (one use each).
+__device__ void coop2_static_update(double* W, long ld, int nrows, int ncols, int c1L, int potr0, int Nb, const double* dinv) {
+    const int lane = threadIdx.x & 31;
+    const long gwarp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, gnwarp = ((long)gridDim.x * blockDim.x) >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int ntr = (nrows + 7) >> 3, ntc = (ncols + 31) >> 5;
+    for (long t = gwarp; t < (long)ntr * ntc; t += gnwarp) {
+        const int r = (int)(t / ntc) * 8 + lr, cb = (int)(t % ntc) * 32;
+        const bool rok = r < nrows;
+        double acc[4][2];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = cb + j * 8 + 2 * lc;
+            acc[j][0] = (rok && c < ncols) ? W[(long)r * ld + c] : 0.0;
+            acc[j][1] = (rok && c + 1 < ncols) ? W[(long)r * ld + c + 1] : 0.0;
+        }
+        const double* arow = W + (long)(rok ? r : 0) * ld + c1L;
+#pragma unroll 4
+        for (int k0 = 0; k0 < Nb; k0 += 4) {
+            const int k = k0 + lc;
+            const bool kok = k < Nb;
+            const double a = (rok && kok) ? -(arow[k] * dinv[k]) : 0.0;
+            const double* brow = W + (long)(potr0 + (kok ? k : 0)) * ld + cb + lr;
+            double b[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = (kok && cb + j * 8 + lr < ncols) ? brow[j * 8] : 0.0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma(acc[j][0], acc[j][1], a, b[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = cb + j * 8 + 2 * lc;
+            if (rok && c < ncols) W[(long)r * ld + c] = acc[j][0];
+            if (rok && c + 1 < ncols) W[(long)r * ld + c + 1] = acc[j][1];
         }
     }
 }

@@ -531,9 +531,9 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
             long long tq0 = clock64();
             if ((int)blockIdx.x == owner) {
                 const int rows = p - k0;
-                if (rows <= kCoopThreads) coop_panel_factor_reg<1>(W, ld, k0, nb, rows, S, sc);
-                else if (rows <= 2 * kCoopThreads) coop_panel_factor_reg<2>(W, ld, k0, nb, rows, S, sc);
-                else coop_panel_factor(W, ld, k0, nb, rows, dsm, prow, S, sc);
+                if (rows <= kCoopThreads) coop_panel_factor_reg<1>(W, ld, k0, nb, rows, rows, S, sc);
+                else if (rows <= 2 * kCoopThreads) coop_panel_factor_reg<2>(W, ld, k0, nb, rows, rows, S, sc);
+                else coop_panel_factor(W, ld, k0, nb, rows, rows, dsm, prow, S, sc);
                 __syncthreads();
                 if (tid == 0 && S.status) { st[0] = (double)((int)st[0] | S.status); S.status = 0; }
                 if (tid == 0) atomicAdd(&cprof[0], (unsigned long long)(clock64() - tq0));
@@ -609,6 +609,187 @@ __global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop(const void* blob,
             HT[(int64_t)n * ldn + N + c] = val;
         }
         grid.sync();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Schur path, geometry stage, grid-cooperative WINDOW elimination with static pivots (few large geometries whose
+// depths decrease outwards, i.e. every boundary is "case 1" of meem_engine.py:170-217 - big_tricylinder).
+// Same window recursion as k_geom_band, but inside window bd the unknowns C1^bd are eliminated FIRST, with the potential
+// rows of boundary bd as pivot rows: their C1 block is the diagonal matrix (h - d_bd) diag R_1n(a_bd) = (h - d_bd) {1/2, 1,
+// 1, ...}, so that step needs no pivot search at all and is one grid-wide DMMA product (coop2_static_update).  Only the
+// C2^bd block (N_bd columns among the N_bd left-over + N_bd+1 velocity rows) goes through the partial-pivot panel
+// machinery of k_geom_coop: (M - 1) N sequential pivot columns instead of (2M - 1) N, on windows instead of the p x p
+// matrix.  Numerical probe against LAPACK's partial pivoting: tools/experiments/exp_static.py (<= 3e-15 on H, u, w, s0).
+// Window layout:  rows [left over (nc) | velocity bd (hv) | c rows (R) | potential bd (Nb)],
+//                 cols [C2^bd (n2) | region bd+1: C1, C2 (or E in the last window) (n1) | b (R) | pad | C1^bd (Nb)].
+struct Coop2Dims { int wrows, wcols; };
+MEEM_HDX void coop2_dims(const Geom& g, const Layout& L, int R, Coop2Dims& D) {
+    D.wrows = D.wcols = 0;
+    int nc = 0;
+    for (int bd = 0; bd < g.M; ++bd) {
+        const bool last = bd == g.M - 1;
+        const int Nb = g.nmk[bd], n2 = bd > 0 ? Nb : 0, n1 = last ? g.nmk[g.M - 1] : 2 * g.nmk[bd + 1];
+        const int hv = last ? 0 : g.nmk[bd + 1];
+        const int rows = nc + hv + R + Nb, cols = ((n2 + n1 + R + 1) & ~1) + Nb;
+        if (rows > D.wrows) D.wrows = rows;
+        if (cols > D.wcols) D.wcols = cols;
+        nc = hv;
+    }
+}
+__host__ __device__ inline int64_t coop2_ld(int wcols) { return (wcols + 1) & ~1; }
+__host__ __device__ inline int64_t coop2_slot_doubles(int wrows, int wcols) {
+    return 2 * (int64_t)wrows * coop2_ld(wcols) + (int64_t)wrows * kCoopNB + kCoopNB * kCoopNB + 2 * kCoopMaxMoves + 16;
+}
+__host__ __device__ inline size_t coop2_smem_bytes(int wrows, int maxN) {
+    const size_t a = (size_t)kCoopNB * (size_t)((wrows + 31) & ~31), b = 2 * (size_t)((maxN + 15) & ~15) + 16, c = (size_t)maxN + 16;
+    return sizeof(double) * (a > b ? (a > c ? a : c) : (b > c ? b : c));
+}
+
+__global__ void __launch_bounds__(kCoopThreads, 1) k_geom_coop2(const void* blob, void* ws, int wrows_max, int wcols_max) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ Layout L;
+    __shared__ CoopShared S;
+    DevView v = make_view(blob, ws);
+    double* dsm = reinterpret_cast<double*>(smem);
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const long gtid = (long)blockIdx.x * nthr + tid, gthr = (long)gridDim.x * nthr;
+    const long ld = coop2_ld(wcols_max);
+    double* Wb[2] = {v.slots, v.slots + (int64_t)wrows_max * ld};
+    CoopScratch sc;
+    sc.Lbuf = v.slots + 2 * (int64_t)wrows_max * ld;
+    sc.L11g = sc.Lbuf + (int64_t)wrows_max * kCoopNB;
+    sc.moves = reinterpret_cast<int*>(sc.L11g + kCoopNB * kCoopNB);
+    for (int item = 0; item < v.hdr->n_geom; ++item) {
+        const int gi = v.order[item];
+        const GeomDesc gd = v.geom[gi];
+        const Geom g = geom_of(v, gd);
+        if (tid == 0) { make_layout(g, L); S.status = 0; }
+        __syncthreads();
+        const int N = gd.N, R = gd.R, M = gd.M;
+        const double* tab = v.tables + gd.tab_off;
+        const uint8_t* flags = v.flags + gd.flag_off;
+        double* gs = v.gstore + gd.gs_off;
+        const int ldn = gs_ldn(N, R);
+        double* HT = gs;
+        double* wv = HT + (int64_t)N * ldn;
+        double* uv = wv + (int64_t)R * N;
+        double* s0 = uv + (int64_t)R * N;
+        double* phi = s0 + R * R;
+        double* bc = phi + R;
+        double* st = bc + R;
+        if (gtid == 0) st[0] = 0.0;
+        int nc = 0, n2o = 0, srows_o = 0;
+        for (int bd = 0; bd < M; ++bd) {
+            const bool last = bd == M - 1;
+            const int Nb = g.nmk[bd], n2 = bd > 0 ? Nb : 0, n1 = last ? N : 2 * g.nmk[bd + 1];
+            const int hv = last ? 0 : g.nmk[bd + 1];
+            const int srows = nc + hv, nsub = srows + R, ncs = n2 + n1 + R, c1L = (ncs + 1) & ~1, potr0 = nsub;
+            const int ncols_w = c1L + Nb, nrows_w = nsub + Nb;
+            double* W = Wb[bd & 1];
+            const double* Wo = Wb[(bd & 1) ^ 1];
+            for (long e = gtid; e < (long)nrows_w * ncols_w; e += gthr) W[(e / ncols_w) * ld + (e % ncols_w)] = 0.0;
+            // reciprocal static pivots (every CTA keeps its own copy): D1_n = (h - d_bd) R_1n(a_bd)
+            {
+                const double hdL = g.h - g.d[bd];
+                const double* TL = tab + L.tab[bd];
+                for (int n = tid; n < Nb; n += nthr) dsm[n] = 1.0 / (hdL * TL[n]);
+            }
+            grid.sync();
+            if (bd > 0) {      // left-over rows and c rows of the previous window: columns [C1^bd | C2^bd | b] there
+                const int sw = 2 * Nb + R;
+                for (long e = gtid; e < (long)(nc + R) * sw; e += gthr) {
+                    const int r = (int)(e / sw), c = (int)(e % sw);
+                    const int ro = r < nc ? n2o + r : srows_o + (r - nc), rn = r < nc ? r : srows + (r - nc);
+                    const int cn = c < Nb ? c1L + c : (c < 2 * Nb ? c - Nb : n2 + n1 + (c - 2 * Nb));
+                    W[(long)rn * ld + cn] = Wo[(long)ro * ld + n2o + c];
+                }
+            } else {
+                for (long e = gtid; e < (long)R * Nb; e += gthr) {
+                    const int j = (int)(e / Nb), n = (int)(e % Nb);
+                    W[(long)(srows + j) * ld + c1L + n] = c_entry(g, L, tab, flags + (long)j * (M + 1), 0, 0, n);
+                }
+            }
+            if (!last) {
+                const int Nr = g.nmk[bd + 1];
+                for (long e = gtid; e < (long)R * n1; e += gthr) {
+                    const int j = (int)(e / n1), c = (int)(e % n1);
+                    W[(long)(srows + j) * ld + n2 + c] =
+                        c_entry(g, L, tab, flags + (long)j * (M + 1), bd + 1, c < Nr ? 0 : 1, c < Nr ? c : c - Nr);
+                }
+            } else {
+                for (long n = gtid; n < n1; n += gthr) W[(long)(potr0 + n) * ld + n2 + n] = 1.0;     // E
+            }
+            fill_A_boundary_at<double>(g, L, tab, bd, W, ld, potr0, nc, c1L, 0, n2, (int)gtid, (int)gthr);
+            for (long e = gtid; e < (long)R * (Nb + hv); e += gthr) {
+                const int i = (int)(e / (Nb + hv)), n = (int)(e % (Nb + hv));
+                const bool vel = n >= Nb;
+                W[(long)(vel ? nc + (n - Nb) : potr0 + n) * ld + n2 + n1 + i] =
+                    b_static_entry(g, L, flags + (long)i * (M + 1), bd, vel, vel ? n - Nb : n);
+            }
+            grid.sync();
+            coop2_static_update(W, ld, nsub, ncs, c1L, potr0, Nb, dsm);
+            grid.sync();
+            int pidx = 0;
+            for (int k0 = 0; k0 < n2; k0 += kCoopNB, ++pidx) {
+                const int nb = min(kCoopNB, n2 - k0);
+                const int owner = (pidx + 7 * bd) % gridDim.x;
+                if ((int)blockIdx.x == owner) {
+                    const int rows = nsub - k0, sr = srows - k0;
+                    if (rows <= kCoopThreads) coop_panel_factor_reg<1>(W, ld, k0, nb, rows, sr, S, sc);
+                    else if (rows <= 2 * kCoopThreads) coop_panel_factor_reg<2>(W, ld, k0, nb, rows, sr, S, sc);
+                    else coop_panel_factor(W, ld, k0, nb, rows, sr, dsm, (wrows_max + 31) & ~31, S, sc);
+                    __syncthreads();
+                    if (tid == 0 && S.status) { st[0] = (double)((int)st[0] | S.status); S.status = 0; }
+                }
+                grid.sync();
+                coop_panel_update(W, ld, nsub, ncs, k0, nb, S, sc, nullptr);
+                __syncthreads();
+                grid.sync();
+            }
+            if (last) {
+                if (n2 > 0) {
+                    coop_backsolve(W, ld, n2, N + R, dsm, S);
+                    __syncthreads();
+                    grid.sync();
+                }
+                // rows of the last region of [G | y0]: C2 rows = rows [0, N) of the window, C1 rows from their pivot rows:
+                // C1_n = (rhs_n - D2_n C2_n) / D1_n.  H[n][n'] = R1'(a)[n] G[C1 n][n'] + R2'(a)[n] G[C2 n][n'], stored transposed
+                const double* TL = tab + L.tab[bd];
+                const double hdL = g.h - g.d[bd];
+                for (long e = gtid; e < (long)N * (N + R); e += gthr) {
+                    const int cidx = (int)(e / N), n = (int)(e % N);
+                    const double d1 = hdL * TL[n];
+                    double g2 = 0.0, rhs = W[(long)(potr0 + n) * ld + n2 + cidx];
+                    if (bd > 0) { g2 = W[(long)n * ld + n2 + cidx]; rhs -= hdL * TL[N + n] * g2; }
+                    double hv2 = TL[2 * N + n] * (rhs / d1);
+                    if (bd > 0) hv2 += TL[3 * N + n] * g2;
+                    if (cidx < N) HT[(int64_t)cidx * ldn + n] = hv2;
+                    else uv[(cidx - N) * N + n] = hv2;
+                }
+                for (long e = gtid; e < (long)R * (N + R); e += gthr) {
+                    const int j = (int)(e / (N + R)), cidx = (int)(e % (N + R));
+                    const double val = -W[(long)(srows + j) * ld + n2 + cidx];
+                    if (cidx < N) wv[j * N + cidx] = val;
+                    else s0[j * R + (cidx - N)] = val;
+                }
+                for (long j = gtid; j < R; j += gthr) {
+                    phi[j] = phi_sum(g, L, tab, flags + (int64_t)j * (M + 1));
+                    bc[j] = b_end_constant(g, flags + (int64_t)j * (M + 1));
+                }
+                grid.sync();
+                for (long e = gtid; e < (long)N * (ldn - N); e += gthr) {
+                    const int n = (int)(e / (ldn - N)), c = (int)(e - (long)n * (ldn - N));
+                    double val = 0.0;
+                    if (c < R) val = uv[c * N + n] + (n == 0 ? bc[c] : 0.0);
+                    else if (c < 2 * R) val = wv[(c - R) * N + n];
+                    HT[(int64_t)n * ldn + N + c] = val;
+                }
+                grid.sync();
+            }
+            n2o = n2; srows_o = srows; nc = hv;
+        }
     }
 }
 
@@ -1970,6 +2151,9 @@ struct meemb200_plan {
     size_t smem_geom, smem_freq, smem_dense, smem_chol, smem_coop, smem_hchol;
     int algo;
     bool use_coop;          // grid-cooperative geometry stage (few large geometries)
+    bool use_coop2;         // ... by window elimination with static pivots for the C1 blocks (k_geom_coop2): every boundary case 1, no X
+    int coop2_wrows, coop2_wcols;
+    size_t smem_coop2;
     int band_variant;       // geometry stage by window elimination (k_geom_band): -1 off, 0 small window in shared memory (128 threads),
                             // 1 window in shared memory (256 threads), 2 window in the CTA's global slot (512 threads)
     int band_wrows, band_wcols, band_grid;
@@ -2049,6 +2233,8 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     int64_t slot_geom = 0, slot_freq = 0, slot_dense = 0;
     int max_p = 1, max_K = 1, max_NT = 1, max_N = 1;
     int band_wrows = 0, band_wcols = 0, band_side = 0;
+    int coop2_wrows = 0, coop2_wcols = 0;
+    bool all_case1 = true;
     double flops = 0.0;
     const int64_t total_regs = b->reg_off[G];
     for (int gi = 0; gi < G; ++gi) {
@@ -2096,6 +2282,10 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
             BandDims D;
             band_dims(g, L, R, D);
             band_wrows = std::max(band_wrows, D.wrows); band_wcols = std::max(band_wcols, D.wcols); band_side = std::max(band_side, D.side);
+            Coop2Dims D2;
+            coop2_dims(g, L, R, D2);
+            coop2_wrows = std::max(coop2_wrows, D2.wrows); coop2_wcols = std::max(coop2_wcols, D2.wcols);
+            for (int i = 0; i + 1 < M; ++i) all_case1 = all_case1 && (b->d[r0 + i] > b->d[r0 + i + 1]);
         }
         slot_freq = std::max<int64_t>(slot_freq, std::max(freq_slot_doubles(gd.N, gd.K, R), freq2_slot_doubles(gd.N, gd.K, R)));
         slot_dense = std::max<int64_t>(slot_dense, 2LL * gd.NT * (gd.NT + R));
@@ -2162,12 +2352,19 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         // single CTA ~6e-8 p^3 ms per geometry, cooperative ~1.5e-3 p ms per geometry)
         const double waves = std::ceil((double)G / ctx->sm_count);
         P->smem_coop = coop_smem_bytes(max_p);
-        P->use_coop = schur && P->smem_coop + 8192 <= limit && (double)G * 1.5e-3 * max_p < waves * 6e-8 * (double)max_p * max_p * max_p;
-        if (getenv("MEEMB200_NO_COOP")) P->use_coop = false;
-        if (getenv("MEEMB200_FORCE_COOP")) P->use_coop = schur && P->smem_coop + 8192 <= limit;   // tests
+        const bool few_large = (double)G * 1.5e-3 * max_p < waves * 6e-8 * (double)max_p * max_p * max_p;
+        bool want_coop = schur && few_large;
+        if (getenv("MEEMB200_NO_COOP")) want_coop = false;
+        if (getenv("MEEMB200_FORCE_COOP")) want_coop = schur;                                      // tests
+        P->use_coop = want_coop && P->smem_coop + 8192 <= limit;
         if (P->use_coop) slot_geom = 0;
         if (P->use_coop)
             for (int gi = 0; gi < G; ++gi) slot_geom = std::max<int64_t>(slot_geom, coop_slot_doubles(P->geoms[gi].p, P->geoms[gi].N, P->geoms[gi].R));
+        // static-pivot window variant: depths decreasing outwards everywhere (the C1 blocks then sit on diagonal pivot blocks), no X
+        P->coop2_wrows = coop2_wrows; P->coop2_wcols = coop2_wcols;
+        P->smem_coop2 = coop2_smem_bytes(coop2_wrows, max_N);
+        P->use_coop2 = want_coop && all_case1 && !b->want_x && P->smem_coop2 + 8192 <= limit && !getenv("MEEMB200_NO_COOP2");
+        if (P->use_coop2) { P->use_coop = true; slot_geom = coop2_slot_doubles(coop2_wrows, coop2_wcols); }
     }
     P->band_variant = -1; P->band_wrows = band_wrows; P->band_wcols = band_wcols; P->band_grid = 0; P->smem_band = 0;
     if (schur && !b->want_x && !P->use_coop && !getenv("MEEMB200_NO_BAND")) {
@@ -2261,7 +2458,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.input_bytes = blob_bytes;
     P->info.workspace_bytes = w;
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x; P->info.n_c = n_c;
-    P->info.geom_kernel = !schur ? -1 : P->use_coop ? 1 : P->band_variant >= 0 ? 2 + P->band_variant : 0;
+    P->info.geom_kernel = !schur ? -1 : P->use_coop2 ? 5 : P->use_coop ? 1 : P->band_variant >= 0 ? 2 + P->band_variant : 0;
     P->info.freq_kernel = !schur ? 3 : b->algo == MEEMB200_ALGO_SCHUR_LU ? 2 : P->use_small ? 1 : 0;
     P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
@@ -2300,7 +2497,18 @@ extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
     return MEEMB200_OK;
 }
 
+static cudaError_t launch_geom_coop2(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(k_geom_coop2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_coop2);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_geom_coop2, kCoopThreads, P->smem_coop2);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    void* args[] = {(void*)&in, (void*)&ws, (void*)&P->coop2_wrows, (void*)&P->coop2_wcols};
+    return cudaLaunchCooperativeKernel((void*)k_geom_coop2, dim3(P->ctx->sm_count), dim3(kCoopThreads), args, P->smem_coop2, s);
+}
 static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
+    if (P->use_coop2) return launch_geom_coop2(P, in, ws, s);
     cudaError_t e = cudaFuncSetAttribute(k_geom_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smem_coop);
     if (e != cudaSuccess) return e;
     int per_sm = 0;

@@ -421,3 +421,40 @@ def test_product_imk_table_entries(ofb):
     got = plan.imk_table(0, 0)
     assert abs(mk[2]) == 1 * np.pi / 2.0                       # the branch is really hit
     assert np.max(np.abs(got - ref)) <= 1e-13 * np.max(np.abs(ref))
+
+
+@pytest.mark.parametrize("env", [{"MEEMB200_FORCE_COOP": "1"}, {"MEEMB200_FORCE_COOP": "1", "MEEMB200_NO_COOP2": "1"}], ids=_ids)
+@pytest.mark.parametrize("name", sorted(META2))
+def test_cooperative_static_window_elimination(ofb, monkeypatch, name, env):
+    """k_geom_coop2 (grid-cooperative window elimination, C1 blocks on their diagonal pivot blocks without a pivot search)
+    forced on every golden sweep of the untouched reference - geometries with an overhang fall back to k_geom_coop - and
+    the pivoted cooperative kernel on the same inputs."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    s = META2[name]
+    geo = ofb.FlatGeometry.from_body_map(s["h"], s["a"], s["d"], s["NMK"], s["body_map"], s["modes"])
+    plan = ofb.BatchPlan([geo, geo], s["omegas"])
+    case1 = all(x > y for x, y in zip(s["d"][:-1], s["d"][1:]))
+    assert plan.geom_kernel == ("k_geom_coop2" if case1 and "MEEMB200_NO_COOP2" not in env else "k_geom_coop")
+    ref = {v: Z2[f"{name}/{v}"] for v in ("added_mass", "damping", "excitation_force", "excitation_phase")}
+    for r in plan.run():
+        assert np.all(r["status"] == 0)
+        _check(r, ref)
+
+
+def test_cooperative_static_unequal_modes_and_many_regions(ofb, monkeypatch):
+    """k_geom_coop2 with unequal mode counts per region (odd block sizes, panels that are not multiples of 16), R = 2, a
+    single cylinder (static step only) and an 8-region staircase, against the oracle."""
+    monkeypatch.setenv("MEEMB200_FORCE_COOP", "1")
+    cases = [(20.0, [5, 10, 15], [15, 10, 5], [30, 12, 25, 40], [0, 1, 1], [0, 1]),
+             (20.0, [5, 10, 15], [15, 10, 5], [33, 47, 21, 9], [0, 0, 1], [0, 1]),
+             (3.0, [1.0], [0.7], [9, 11], [0], [0]),
+             (10.0, [0.75 * (i + 1) for i in range(8)], [6.0 - 0.6 * i for i in range(8)], [14] * 9, [0] * 8, [0])]
+    om = np.array([0.4, 1.3, 2.6])
+    for c in cases:
+        geo = ofb.FlatGeometry.from_body_map(*c)
+        plan = ofb.BatchPlan([geo], om)
+        assert plan.geom_kernel == "k_geom_coop2"
+        res = plan.run()[0]
+        assert np.all(res["status"] == 0)
+        _check(res, mo.run_sweep(mo.FlatGeometry(*c[:4]), om, c[4], c[5]))
