@@ -399,9 +399,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_geom(const void* blob, void* 
 // Schur path, geometry stage by window elimination (meem_geom_band.cuh): one CTA per geometry, the window in shared
 // memory (SMEMWIN: dynamic smem = LU scratch | window | hand-over buffer) or in the CTA's L2-resident global slot.
 // Used whenever X is not requested (the X reconstruction needs all of G, which only the dense elimination forms).
+constexpr int kBandSmallChunk = 72;      // U12 staging chunk of the small variant (>= the 65 window columns of N = 16, R = 1)
 __host__ __device__ inline int band_ld(int wcols, bool smem) { return smem ? (wcols | 1) : ((wcols + 1) & ~1); }
 template <int NB, int THREADS, int MINB, bool SMALL, bool SMEMWIN, int CHUNK>
-__global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, void* ws, int wrows_max, int wcols_max) {
+__global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, void* ws, int wrows_max, int wcols_max, int side_alias) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ int sh_item, sh_status;
@@ -410,7 +411,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, v
     const long ld = band_ld(wcols_max, SMEMWIN);
     const size_t lu_bytes = (lu_smem_bytes<double, NB, CHUNK>(wrows_max) + 15) & ~(size_t)15;
     double* W = SMEMWIN ? reinterpret_cast<double*>(smem + lu_bytes) : v.slots + (int64_t)blockIdx.x * v.hdr->slot_doubles_geom;
-    double* side = W + (long)wrows_max * ld;
+    // the hand-over buffer between two windows is only live while no elimination runs: it may share the LU scratch
+    double* side = side_alias ? reinterpret_cast<double*>(smem) : W + (long)wrows_max * ld;
     for (;;) {
         const int item = next_item(&v.counters[0], &sh_item);
         if (item >= v.hdr->n_geom) break;
@@ -2156,7 +2158,7 @@ struct meemb200_plan {
     size_t smem_coop2;
     int band_variant;       // geometry stage by window elimination (k_geom_band): -1 off, 0 small window in shared memory (128 threads),
                             // 1 window in shared memory (256 threads), 2 window in the CTA's global slot (512 threads)
-    int band_wrows, band_wcols, band_grid;
+    int band_wrows, band_wcols, band_grid, band_side_alias;
     size_t smem_band;
     int64_t wave_items;     // systems per frequency-stage wave
     int n_waves, solve_grid;
@@ -2370,12 +2372,16 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     if (schur && !b->want_x && !P->use_coop && !getenv("MEEMB200_NO_BAND")) {
         // window elimination instead of the dense p x p LU (meem_geom_band.cuh); X needs all of G and keeps the dense form
         const size_t win_s = 8 * ((size_t)band_wrows * band_ld(band_wcols, true) + band_side);
-        const size_t s0 = align_up(lu_smem_bytes<double, 8, 128>(band_wrows), 16) + win_s;
+        // small variant: the hand-over buffer aliases the LU scratch when it fits there (6 instead of 5 CTAs per SM on the C4 sweep)
+        const size_t lu0 = align_up(lu_smem_bytes<double, 8, kBandSmallChunk>(band_wrows), 16);
+        const bool alias0 = 8 * (size_t)band_side + 64 <= lu0;
+        const size_t s0 = lu0 + (alias0 ? 8 * (size_t)band_wrows * band_ld(band_wcols, true) : win_s);
+        P->band_side_alias = 0;
         const size_t s1 = align_up(lu_smem_bytes<double, 8, kLuChunk>(band_wrows), 16) + win_s;
         const size_t s2 = align_up(lu_smem_bytes<double, 8, kLuChunk>(band_wrows), 16);
         int want = -1;
         if (const char* ev = getenv("MEEMB200_BAND_VARIANT")) want = atoi(ev);     // tuning / test override
-        if ((want < 0 || want == 0) && s0 + 2048 <= limit / 4) { P->band_variant = 0; P->smem_band = s0; }
+        if ((want < 0 || want == 0) && s0 + 2048 <= limit / 4) { P->band_variant = 0; P->smem_band = s0; P->band_side_alias = alias0 ? 1 : 0; }
         else if ((want < 0 || want == 1 || want == 0) && s1 + 2048 <= limit) { P->band_variant = 1; P->smem_band = s1; }
         else if (s2 + 2048 <= limit) { P->band_variant = 2; P->smem_band = s2; }
         if (P->band_variant >= 0) slot_geom = P->band_variant == 2 ? (int64_t)band_wrows * band_ld(band_wcols, false) + band_side : 0;
@@ -2519,8 +2525,8 @@ static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, 
     return cudaLaunchCooperativeKernel((void*)k_geom_coop, dim3(P->ctx->sm_count), dim3(kCoopThreads), args, P->smem_coop, s);
 }
 static cudaError_t launch_geom_band(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
-    typedef void (*band_fn)(const void*, void*, int, int);
-    static const band_fn fns[3] = {k_geom_band<8, 128, 4, true, true, 128>, k_geom_band<8, 256, 2, false, true, kLuChunk>,
+    typedef void (*band_fn)(const void*, void*, int, int, int);
+    static const band_fn fns[3] = {k_geom_band<8, 128, 6, true, true, kBandSmallChunk>, k_geom_band<8, 256, 2, false, true, kLuChunk>,
                                    k_geom_band<8, 512, 1, false, false, kLuChunk>};
     static const int thr[3] = {128, 256, 512};
     const band_fn kfn = fns[P->band_variant];
@@ -2534,7 +2540,7 @@ static cudaError_t launch_geom_band(meemb200_plan* P, const void* in, void* ws, 
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
         P->band_grid = P->band_variant == 2 ? P->n_slots_geom : (int)std::min<int64_t>(P->hdr()->n_geom, (int64_t)per_sm * P->ctx->sm_count);
     }
-    kfn<<<P->band_grid, nthr, P->smem_band, s>>>(in, ws, P->band_wrows, P->band_wcols);
+    kfn<<<P->band_grid, nthr, P->smem_band, s>>>(in, ws, P->band_wrows, P->band_wcols, P->band_side_alias);
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
