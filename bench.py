@@ -236,7 +236,7 @@ def kernel_flops(flat, F_, algo, factorised, geom_kernel):
 class Runner:
     """One workload on the process group through the product entry (ShardedPlan): timed steps, e2e, stage times."""
 
-    def __init__(self, ofb, name, world, rank, dev, algo, flush):
+    def __init__(self, ofb, name, world, rank, dev, algo, flush, gather="all"):
         import torch
         from openflash_b200.distributed import ShardedPlan
         self.torch, self.ofb, self.name, self.world, self.rank, self.dev, self.algo, self.flush = torch, ofb, name, world, rank, dev, algo, flush
@@ -245,7 +245,7 @@ class Runner:
         t0 = time.perf_counter()
         flat = [ofb.FlatGeometry.from_body_map(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"]) for g in geoms]
         algo_id = {"schur": ofb.ALGO_SCHUR, "schur_lu": ofb.ALGO_SCHUR_LU, "dense": ofb.ALGO_DENSE}[algo]
-        self.sp = ShardedPlan(flat, omegas, algo=algo_id, device=dev.index)
+        self.sp = ShardedPlan(flat, omegas, algo=algo_id, device=dev.index, gather=gather)
         self.plan_ms = 1e3 * (time.perf_counter() - t0)
         self.flat = flat
         self.total_sys = len(geoms) * len(omegas)
@@ -291,10 +291,10 @@ class Runner:
             self.sp.upload()
             self.sp.solve()
             packed = self.sp.download_packed()          # every output of every rank in host memory (pinned), one copy
-            checksum = int(packed[::4096].sum())         # the host really reads the result buffer
+            checksum = int(packed[::4096].sum()) if packed is not None else 0      # the host really reads the result buffer
             torch.cuda.synchronize()
             ms += 1e3 * (time.perf_counter() - t0)
-        self.res = self.sp.download()                    # per-geometry dicts (host post-processing, not timed)
+        self.res = self.sp.download() or []              # per-geometry dicts (host post-processing, not timed); None off-root
         self.checksum = checksum
         return ms
 
@@ -440,20 +440,26 @@ def main():
     extra = {}
     if not args.no_extra and args.algo == "schur":
         # north star: the 10^6-system sweep as a fixed total over the N GPUs (cost-balanced geometry shards + one gather)
-        sw = Runner(ofb, "sweep_1e6", world, rank, dev, "schur", flush)
+        sw = Runner(ofb, "sweep_1e6", world, rank, dev, "schur", flush, gather="root")
         ksw = max(args.steps, 3)
         sw_ms = sw.timed(ksw, 3)
         local_ms = float(np.mean([s["roots"] + s["geometry"] + s["frequency"] for s in sw.stage]))
         sw_e2e_ms = sw.e2e(2)
         per_rank = sw.gather_all(local_ms)
         sw_ms, sw_e2e_ms = sw.reduce_max([sw_ms, sw_e2e_ms])
+        failed = sw.reduce_max([float(sum(np.count_nonzero(r["status"]) for r in sw.res))])[0]
         extra["sweep_1e6"] = {"systems": sw.total_sys, "scaling": "strong", "value": sw.total_sys * ksw / (sw_ms * 1e-3), "unit": UNIT,
                               "ms_per_step": sw_ms / ksw, "per_rank_kernel_ms": [round(x, 4) for x in per_rank],
                               "gather_ms": round(sw_ms / ksw - max(per_rank), 4),
+                              "gather": "NCCL gather of the packed output buffers to rank 0 (the path's only exchange)",
                               "e2e": {"value": sw.total_sys * 2 / (sw_e2e_ms * 1e-3), "ms_per_step": sw_e2e_ms / 2,
-                                      "includes": "H2D inputs, kernels, gather, D2H of all ranks' outputs on every rank"},
-                              "plan_ms_once": round(sw.plan_ms, 1), "workload": sw.desc,
-                              "failed_systems": int(sum(np.count_nonzero(r["status"]) for r in sw.res))}
+                                      "includes": "H2D inputs, kernels, gather, one pinned D2H of every rank's outputs on rank 0"},
+                              "plan_ms_once": round(sw.plan_ms, 1), "workload": sw.desc, "failed_systems": int(failed)}
+        if world > 1:       # the same sweep with results delivered to EVERY rank (all_gather)
+            sw2 = Runner(ofb, "sweep_1e6", world, rank, dev, "schur", flush, gather="all")
+            ms2 = sw2.reduce_max([sw2.timed(ksw, 3)])[0]
+            extra["sweep_1e6"]["value_all_gather"] = sw2.total_sys * ksw / (ms2 * 1e-3)
+            del sw2
         del sw
 
     if rank == 0:

@@ -79,7 +79,8 @@ class ShardedPlan:
     so no sizes are exchanged.
     """
 
-    def __init__(self, geometries, freqs, group=None, plan_factory=None, want_c=False, want_x=False, **plan_kw):
+    def __init__(self, geometries, freqs, group=None, plan_factory=None, want_c=False, want_x=False, gather="all", root=0,
+                 **plan_kw):
         import torch
         import torch.distributed as dist
         from .batch import BatchPlan, output_layout
@@ -89,6 +90,9 @@ class ShardedPlan:
         self.geometries = list(geometries)
         self.freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
         self.want_c, self.want_x = bool(want_c), bool(want_x)
+        if gather not in ("all", "root"):
+            raise ValueError("gather must be 'all' (every rank receives every result) or 'root' (only rank `root` does)")
+        self.gather_mode, self.root = gather, int(root)
         G, F, W = len(self.geometries), len(self.freqs), self.world
         self.mode, _ = plan_shards(G, F, W)
         if self.mode == "geometry":
@@ -111,8 +115,9 @@ class ShardedPlan:
         self.local = factory(my_geos, self.freqs[f0:f1], want_c=self.want_c, want_x=self.want_x,
                              out_bytes_min=self.slot_bytes, **plan_kw) if (len(my_geos) and f1 > f0) else None
         dev = self.local.d_out.device if self.local is not None else torch.device("cpu")
-        self.gathered = torch.empty(self.slot_bytes * W, dtype=torch.uint8, device=dev) if W > 1 else None
-        self.h_gathered = (torch.empty(self.slot_bytes * W, dtype=torch.uint8, pin_memory=dev.type == "cuda") if W > 1 else None)
+        holds_all = W > 1 and (gather == "all" or self.rank == self.root)
+        self.gathered = torch.empty(self.slot_bytes * W, dtype=torch.uint8, device=dev) if holds_all else None
+        self.h_gathered = (torch.empty(self.slot_bytes * W, dtype=torch.uint8, pin_memory=dev.type == "cuda") if holds_all else None)
         self._empty = torch.zeros(self.slot_bytes, dtype=torch.uint8, device=dev) if self.local is None else None
 
     def upload(self):
@@ -125,11 +130,18 @@ class ShardedPlan:
             self.local.solve()
         if self.world > 1:
             src = self.local.d_out if self.local is not None else self._empty
-            self.dist.all_gather_into_tensor(self.gathered, src, group=self.group)
+            if self.gather_mode == "all":
+                self.dist.all_gather_into_tensor(self.gathered, src, group=self.group)
+            else:       # one receiver: 1 / world of the all-gather's traffic per link
+                dst = self.dist.get_global_rank(self.group, self.root) if self.group is not None else self.root
+                parts = list(self.gathered.view(self.world, self.slot_bytes).unbind(0)) if self.rank == self.root else None
+                self.dist.gather(src, parts, dst=dst, group=self.group)
 
     def download_packed(self):
         """ONE device->host copy of every rank's packed outputs into pinned memory; returns the uint8 host buffer
         (rank r's slot at r * slot_bytes, laid out by ``layouts[r]``).  `download` turns it into per-geometry dicts."""
+        if self.gathered is None and self.world > 1:
+            return None                               # gather="root": only the root rank holds the results
         if self.world == 1:
             self.local.h_out.copy_(self.local.d_out, non_blocking=True)
             self.torch.cuda.current_stream(self.local.device).synchronize()
@@ -145,6 +157,8 @@ class ShardedPlan:
         if self.world == 1:
             return self.local.split(self.local.download())
         host = self.download_packed()
+        if host is None:
+            return None
         G, F = len(self.geometries), len(self.freqs)
         per_geom = [[None] * self.world for _ in range(G)]
         for r in range(self.world):

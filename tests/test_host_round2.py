@@ -154,6 +154,13 @@ def _sharded_worker(rank, world, port, tmp):
     sp2 = ShardedPlan(geos[:1], om2, plan_factory=_FakePlan)
     res2 = sp2.run()
     ok &= sp2.mode == "frequency" and bool(np.allclose(res2[0]["added_mass"][:, 0, 0], 1000 + om2))
+    # gather="root": only rank 1 receives
+    sp3 = ShardedPlan(geos, om, plan_factory=_FakePlan, gather="root", root=1)
+    res3 = sp3.run()
+    if rank == 1:
+        ok &= all(bool(np.allclose(r["added_mass"][:, 0, 0], g.h * 1000 + om)) for g, r in zip(geos, res3))
+    else:
+        ok &= res3 is None
     with open(os.path.join(tmp, f"ok{rank}"), "w") as f:
         f.write("1" if ok else "0")
     dist.destroy_process_group()
