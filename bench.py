@@ -212,6 +212,27 @@ def band_flops(g):
     return fl
 
 
+def coop2_flops(g):
+    """Closed-form real FP64 flops of the static-pivot window elimination (k_geom_coop2): per window one rank-N_bd product
+    for the C1 block, the partial-pivot elimination of the C2 block, and the back-substitution of the last window."""
+    nmk = [int(x) for x in g.NMK]
+    M, R = len(nmk) - 1, int(g.R)
+    fl, nc = 0.0, 0
+    for bd in range(M):
+        last = bd == M - 1
+        Nb, n2 = nmk[bd], (nmk[bd] if bd > 0 else 0)
+        n1 = nmk[M - 1] if last else 2 * nmk[bd + 1]
+        hv = 0 if last else nmk[bd + 1]
+        nsub, ncs = nc + hv + R, n2 + n1 + R
+        fl += 2.0 * nsub * Nb * ncs
+        k = np.arange(n2, dtype=float)
+        fl += float(np.sum(2.0 * (nsub - 1 - k) * (ncs - 1 - k)))
+        if last:
+            fl += float(n2) * n2 * (n1 + R)
+        nc = hv
+    return fl
+
+
 def kernel_flops(flat, F_, algo, factorised, geom_kernel):
     """Closed-form real FP64 flops per kernel family for one step over geometries `flat` x F_ frequencies."""
     kf = {}
@@ -221,7 +242,8 @@ def kernel_flops(flat, F_, algo, factorised, geom_kernel):
         if algo == "dense":
             d = {"frequency": F_ * (8 / 3 * NT ** 3 + 8 * NT * NT * R)}
         else:
-            geom = band_flops(g) if geom_kernel.startswith("k_geom_band") else 2 / 3 * p ** 3 + 2 * p * p * (N + R)
+            geom = (band_flops(g) if geom_kernel.startswith("k_geom_band") else coop2_flops(g) if geom_kernel == "k_geom_coop2"
+                    else 2 / 3 * p ** 3 + 2 * p * p * (N + R))
             if algo == "schur":
                 gemm = (N * N * K + 4 * R * N * K + N * K * K) if factorised else (2 * N * N * K + N * K * K)
                 d = {"geometry": geom + (N ** 3 / 3 if factorised else 0.0), "freq_gemm": F_ * gemm,
