@@ -22,6 +22,7 @@ import subprocess
 import sys
 import threading
 import time
+from types import SimpleNamespace
 
 import numpy as np
 
@@ -265,11 +266,12 @@ class Runner:
         geoms, omegas, self.desc, self.scaling = global_workload(name, world)
         self.geoms, self.omegas = geoms, omegas
         t0 = time.perf_counter()
-        flat = [ofb.FlatGeometry.from_body_map(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"]) for g in geoms]
+        batch = ofb.GeometryBatch.from_dicts(geoms)          # packed arrays (no Python object per geometry)
         algo_id = {"schur": ofb.ALGO_SCHUR, "schur_lu": ofb.ALGO_SCHUR_LU, "dense": ofb.ALGO_DENSE}[algo]
-        self.sp = ShardedPlan(flat, omegas, algo=algo_id, device=dev.index, gather=gather)
+        self.sp = ShardedPlan(batch, omegas, algo=algo_id, device=dev.index, gather=gather)
         self.plan_ms = 1e3 * (time.perf_counter() - t0)
-        self.flat = flat
+        self.flat = [SimpleNamespace(NMK=g["NMK"], R=len(g["modes"]), size=int(g["NMK"][0] + g["NMK"][-1] + 2 * sum(g["NMK"][1:-1])))
+                     for g in geoms]
         self.total_sys = len(geoms) * len(omegas)
 
     def step(self):

@@ -65,6 +65,119 @@ class FlatGeometry:
         return cls(h, a, d, NMK, flags)
 
 
+class GeometryBatch:
+    """Many geometries as packed arrays - exactly the CSR layout of `MeemBatch` (include/meemb200.h): per geometry M + 1
+    entries of a / d / nmk (the exterior's a = inf, d = 0 included) from reg_off[g], and R_g * (M_g + 1) heaving flags from
+    flag_off[g].  Design sweeps build this once with array arithmetic instead of one Python object per geometry;
+    `BatchPlan` and `ShardedPlan` accept it wherever they accept a list of `FlatGeometry`."""
+
+    def __init__(self, h, reg_off, a, d, nmk, n_modes, flag_off, flags):
+        self.h = np.ascontiguousarray(h, dtype=np.float64)
+        self.reg_off = np.ascontiguousarray(reg_off, dtype=np.int32)
+        self.a = np.ascontiguousarray(a, dtype=np.float64)
+        self.d = np.ascontiguousarray(d, dtype=np.float64)
+        self.nmk = np.ascontiguousarray(nmk, dtype=np.int32)
+        self.n_modes = np.ascontiguousarray(n_modes, dtype=np.int32)
+        self.flag_off = np.ascontiguousarray(flag_off, dtype=np.int64)
+        self.flags = np.ascontiguousarray(flags, dtype=np.uint8)
+        G = len(self.h)
+        if len(self.reg_off) != G + 1 or len(self.flag_off) != G + 1 or len(self.n_modes) != G:
+            raise ValueError("inconsistent packed geometry arrays")
+        self.M = (np.diff(self.reg_off) - 1).astype(np.int32)
+        nmk64 = self.nmk.astype(np.int64)
+        tot = np.add.reduceat(nmk64, self.reg_off[:-1])                      # sum of all M + 1 entries
+        first, last = nmk64[self.reg_off[:-1]], nmk64[self.reg_off[1:] - 1]
+        self.K = last
+        self.N = nmk64[self.reg_off[1:] - 2]
+        self.NT = 2 * tot - first - last                                       # N_0 + 2 sum N_1..M-1 + K (meem_engine.py:116)
+        self.R = self.n_modes
+
+    def __len__(self):
+        return len(self.h)
+
+    @classmethod
+    def from_list(cls, geos):
+        geos = list(geos)
+        G = len(geos)
+        M = np.fromiter((len(g.a) for g in geos), dtype=np.int64, count=G)
+        R = np.fromiter((g.mode_flags.shape[0] for g in geos), dtype=np.int64, count=G)
+        reg_off = np.zeros(G + 1, dtype=np.int64)
+        np.cumsum(M + 1, out=reg_off[1:])
+        total = int(reg_off[-1])
+        interior = np.ones(total, dtype=bool)
+        interior[reg_off[1:] - 1] = False
+        a = np.full(total, np.inf)
+        d = np.zeros(total)
+        a[interior] = np.concatenate([g.a for g in geos])
+        d[interior] = np.concatenate([g.d for g in geos])
+        nmk = np.concatenate([g.NMK for g in geos])
+        h = np.fromiter((g.h for g in geos), dtype=np.float64, count=G)
+        flag_off = np.zeros(G + 1, dtype=np.int64)
+        np.cumsum(R * (M + 1), out=flag_off[1:])
+        flags = np.zeros(int(flag_off[-1]), dtype=np.uint8)
+        if np.all(R == 1):
+            flags[interior] = np.concatenate([g.mode_flags.ravel() for g in geos])
+        else:
+            for gi, g in enumerate(geos):
+                fl = np.zeros((g.R, g.M + 1), dtype=np.uint8)
+                fl[:, :g.M] = g.mode_flags
+                flags[flag_off[gi]:flag_off[gi + 1]] = fl.ravel()
+        return cls(h, reg_off, a, d, nmk, R, flag_off, flags)
+
+    @classmethod
+    def from_dicts(cls, dicts):
+        """From dicts with keys h, a, d, NMK, body_map, modes (bench.py's workload generators): body b moves all its
+        regions.  Single-mode dicts are packed with array arithmetic only."""
+        dicts = list(dicts)
+        if not all(len(g["modes"]) == 1 for g in dicts):
+            out = []
+            for g in dicts:
+                bm = np.asarray(g["body_map"])
+                fl = np.array([[1 if b == m else 0 for b in bm] for m in g["modes"]], dtype=np.uint8)
+                out.append(FlatGeometry(g["h"], g["a"], g["d"], g["NMK"], fl))
+            return cls.from_list(out)
+        G = len(dicts)
+        M = np.fromiter((len(g["a"]) for g in dicts), dtype=np.int64, count=G)
+        reg_off = np.zeros(G + 1, dtype=np.int64)
+        np.cumsum(M + 1, out=reg_off[1:])
+        total = int(reg_off[-1])
+        interior = np.ones(total, dtype=bool)
+        interior[reg_off[1:] - 1] = False
+        a = np.full(total, np.inf)
+        d = np.zeros(total)
+        a[interior] = np.concatenate([np.asarray(g["a"], dtype=np.float64) for g in dicts])
+        d[interior] = np.concatenate([np.asarray(g["d"], dtype=np.float64) for g in dicts])
+        nmk = np.concatenate([np.asarray(g["NMK"], dtype=np.int32) for g in dicts])
+        if len(nmk) != total or len(a[interior]) != total - G:
+            raise ValueError("need len(a) == len(d) == len(NMK) - 1 for every geometry")
+        h = np.fromiter((g["h"] for g in dicts), dtype=np.float64, count=G)
+        bm = np.concatenate([np.asarray(g["body_map"], dtype=np.int64) for g in dicts])
+        mode = np.repeat(np.fromiter((g["modes"][0] for g in dicts), dtype=np.int64, count=G), M)
+        flags = np.zeros(total, dtype=np.uint8)
+        flags[interior] = (bm == mode).astype(np.uint8)
+        return cls(h, reg_off, a, d, nmk, np.ones(G, dtype=np.int32), reg_off.copy(), flags)
+
+    def take(self, idx):
+        """Sub-batch of the geometries `idx` (array of indices), packed again - vectorised CSR gather."""
+        idx = np.asarray(idx, dtype=np.int64)
+        ln = (self.M[idx] + 1).astype(np.int64)
+        new_off = np.zeros(len(idx) + 1, dtype=np.int64)
+        np.cumsum(ln, out=new_off[1:])
+        src = np.repeat(self.reg_off[idx].astype(np.int64) - new_off[:-1], ln) + np.arange(int(new_off[-1]))
+        fln = self.n_modes[idx].astype(np.int64) * ln
+        new_foff = np.zeros(len(idx) + 1, dtype=np.int64)
+        np.cumsum(fln, out=new_foff[1:])
+        fsrc = np.repeat(self.flag_off[idx] - new_foff[:-1], fln) + np.arange(int(new_foff[-1]))
+        return GeometryBatch(self.h[idx], new_off, self.a[src], self.d[src], self.nmk[src], self.n_modes[idx], new_foff, self.flags[fsrc])
+
+    def costs(self, n_freq):
+        """Relative device cost per geometry: window elimination (~25 N^3 per interior boundary) + n_freq Schur stages."""
+        n3 = self.nmk.astype(np.float64) ** 3
+        geom = 25.0 * (np.add.reduceat(n3, self.reg_off[:-1]) - self.K.astype(np.float64) ** 3)
+        N, K = self.N.astype(np.float64), self.K.astype(np.float64)
+        return geom + n_freq * (N * N * K + N * K * K + K ** 3 / 3.0)
+
+
 def output_layout(F, R, NT, K, want_c=False, want_x=False):
     """Byte layout of the packed output buffer of a batch: {name: (offset, nbytes)}, total bytes.  R, NT, K are the
     per-geometry mode counts, system sizes and exterior mode counts.  Pure host arithmetic: every rank of a sharded
@@ -152,38 +265,25 @@ class BatchPlan:
         self.device_index = int(device)
         self.ctx = get_context(self.device_index)
         self.device = torch.device("cuda", self.device_index)
-        geometries = list(geometries)
-        if not geometries:
+        gb = geometries if isinstance(geometries, GeometryBatch) else None
+        if gb is None:
+            geometries = list(geometries)
+            if not geometries:
+                raise ValueError("empty batch")
+            gb = GeometryBatch.from_list(geometries)
+        if len(gb) == 0:
             raise ValueError("empty batch")
-        self.G = len(geometries)
+        self.batch = gb
+        self.G = len(gb)
         self.freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).ravel())
         self.F = len(self.freqs)
-        self.R = np.array([g.R for g in geometries], dtype=np.int32)
-        self.M = np.array([g.M for g in geometries], dtype=np.int32)
-        self.NT = np.array([g.size for g in geometries], dtype=np.int64)
+        self.R = gb.R
+        self.M = gb.M
+        self.NT = gb.NT
         self.want_x = bool(want_x)
         self.want_c = bool(want_c)
         self.algo = int(algo)
-        reg_off = np.zeros(self.G + 1, dtype=np.int32)
-        np.cumsum(self.M + 1, out=reg_off[1:])
-        flag_off = np.zeros(self.G + 1, dtype=np.int64)
-        np.cumsum(self.R.astype(np.int64) * (self.M + 1), out=flag_off[1:])
-        a = np.empty(reg_off[-1], dtype=np.float64)
-        d = np.empty(reg_off[-1], dtype=np.float64)
-        nmk = np.empty(reg_off[-1], dtype=np.int32)
-        flags = np.zeros(flag_off[-1], dtype=np.uint8)
-        h = np.empty(self.G, dtype=np.float64)
-        for gi, g in enumerate(geometries):
-            r0, M = reg_off[gi], g.M
-            a[r0:r0 + M] = g.a
-            a[r0 + M] = np.inf
-            d[r0:r0 + M] = g.d
-            d[r0 + M] = 0.0
-            nmk[r0:r0 + M + 1] = g.NMK
-            h[gi] = g.h
-            fl = np.zeros((g.R, M + 1), dtype=np.uint8)
-            fl[:, :M] = g.mode_flags
-            flags[flag_off[gi]:flag_off[gi + 1]] = fl.ravel()
+        reg_off, h, a, d, nmk, flag_off, flags = gb.reg_off, gb.h, gb.a, gb.d, gb.nmk, gb.flag_off, gb.flags
         self._keep = (reg_off, h, a, d, nmk, self.R, flag_off, flags)
         b = _lib.MeemBatch()
         b.n_geom, b.n_freq = self.G, self.F
@@ -206,7 +306,7 @@ class BatchPlan:
         nb = int(self.info.input_bytes)
         self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
         self._refresh_host_blob()
-        self.K = np.array([int(g.NMK[-1]) for g in geometries], dtype=np.int64)
+        self.K = gb.K
         self._seg, self._out_bytes = output_layout(self.F, self.R, self.NT, self.K, self.want_c, self.want_x)
         self._out_bytes = max(self._out_bytes, int(out_bytes_min))
         with torch.cuda.device(self.device):
@@ -311,6 +411,19 @@ class BatchPlan:
         self.h_out.copy_(self.d_out, non_blocking=True)
         t.cuda.current_stream(self.device).synchronize()
         return unpack_outputs(self.h_out.numpy(), self._seg, self.G, self.F, self.want_c, self.want_x, copy)
+
+    def download_stacked(self, copy=False):
+        """For batches whose geometries all have the same number of modes R: the outputs as arrays with a leading geometry
+        axis - added_mass / damping [G, F, R, R], excitation_force / excitation_phase [G, F, R], m0 / status [G, F] - without
+        a Python loop over geometries (design sweeps).  Views of the pinned download buffer unless copy=True."""
+        R = int(self.R[0])
+        if np.any(self.R != R):
+            raise ValueError("download_stacked needs the same number of modes for every geometry")
+        flat = self.download(copy=copy)
+        G, F = self.G, self.F
+        return dict(added_mass=flat["added_mass"].reshape(G, F, R, R), damping=flat["damping"].reshape(G, F, R, R),
+                    excitation_force=flat["excitation_force"].reshape(G, F, R), excitation_phase=flat["excitation_phase"].reshape(G, F, R),
+                    m0=flat["m0"], status=flat["status"])
 
     def run(self):
         self.upload()

@@ -10,7 +10,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import openflash_b200 as ofb
-from openflash_b200.batch import output_layout, split_outputs, unpack_outputs
+from openflash_b200.batch import GeometryBatch, output_layout, split_outputs, unpack_outputs
 from openflash_b200.distributed import ShardedPlan, geometry_cost
 
 
@@ -102,11 +102,10 @@ class _FakePlan:
     """Stand-in for BatchPlan on CPU tensors: 'solves' by writing a value that encodes (geometry, frequency) identity."""
 
     def __init__(self, geometries, freqs, want_c=False, want_x=False, out_bytes_min=0, **kw):
-        self.geos, self.freqs = list(geometries), np.asarray(freqs)
-        self.F, self.G = len(self.freqs), len(self.geos)
-        self.R = [g.R for g in self.geos]
-        self.NT = [g.size for g in self.geos]
-        self.K = [int(g.NMK[-1]) for g in self.geos]
+        gb = geometries if isinstance(geometries, GeometryBatch) else GeometryBatch.from_list(geometries)
+        self.gb, self.freqs = gb, np.asarray(freqs)
+        self.F, self.G = len(self.freqs), len(gb)
+        self.R, self.NT, self.K = gb.R, gb.NT, gb.K
         self.want_c, self.want_x = want_c, want_x
         self.seg, nbytes = output_layout(self.F, self.R, self.NT, self.K, want_c, want_x)
         self.d_out = torch.zeros(max(nbytes, out_bytes_min), dtype=torch.uint8)
@@ -117,14 +116,15 @@ class _FakePlan:
     def solve(self):
         buf = self.d_out.numpy()
         am = []
-        for g in self.geos:
+        for h, R in zip(self.gb.h, self.gb.R):
             for w in self.freqs:
-                am += [g.h * 1000 + w + 0.01 * (j * g.R + i) for j in range(g.R) for i in range(g.R)]
+                am += [h * 1000 + w + 0.01 * (j * R + i) for j in range(R) for i in range(R)]
         off, n = self.seg["added_mass"]
         buf[off:off + n].view(np.float64)[:] = am
         if self.want_c:
             off, n = self.seg["c_vector"]
-            buf[off:off + n].view(np.float64)[:] = np.concatenate([np.full(g.R * (g.size - int(g.NMK[-1])), g.h) for g in self.geos])
+            buf[off:off + n].view(np.float64)[:] = np.concatenate([np.full(int(R * (NT - K)), h) for h, R, NT, K in
+                                                                    zip(self.gb.h, self.R, self.NT, self.K)])
 
     def download(self):
         return unpack_outputs(self.d_out.numpy(), self.seg, self.G, self.F, self.want_c, self.want_x)
@@ -178,3 +178,27 @@ def test_geometry_cost_orders_by_size():
     small = ofb.FlatGeometry(50.0, [1.0, 2.0], [5.0, 2.0], [16] * 3)
     big = ofb.FlatGeometry(50.0, np.arange(1.0, 9.0), np.linspace(20, 2, 8), [16] * 9)
     assert geometry_cost(big, 64) > geometry_cost(small, 64) > 0
+
+
+def test_geometry_batch_packing_take_and_costs():
+    """Packed batch == per-geometry flattening (meem_engine.py:110-116): exterior a = inf / d = 0 appended, flags padded,
+    N_T = N_0 + 2 sum N_i + K; `take` re-packs a subset; costs grow with size."""
+    geos = [ofb.FlatGeometry(float(i + 1), np.arange(1, 2 + i % 3, dtype=float), np.linspace(0.5, 0.2, 1 + i % 3), [4 + i] * (2 + i % 3),
+                             [[1] * (1 + i % 3)] * (1 + i % 2)) for i in range(9)]
+    gb = GeometryBatch.from_list(geos)
+    assert len(gb) == 9 and list(gb.M) == [g.M for g in geos] and list(gb.NT) == [g.size for g in geos]
+    assert list(gb.K) == [int(g.NMK[-1]) for g in geos] and list(gb.N) == [int(g.NMK[-2]) for g in geos]
+    for gi, g in enumerate(geos):
+        r0, r1 = gb.reg_off[gi], gb.reg_off[gi + 1]
+        assert np.array_equal(gb.a[r0:r1 - 1], g.a) and np.isinf(gb.a[r1 - 1]) and gb.d[r1 - 1] == 0.0
+        assert np.array_equal(gb.nmk[r0:r1], g.NMK)
+        fl = gb.flags[gb.flag_off[gi]:gb.flag_off[gi + 1]].reshape(g.R, g.M + 1)
+        assert np.array_equal(fl[:, :g.M], g.mode_flags) and np.all(fl[:, g.M] == 0)
+    sub = gb.take([7, 2, 5])
+    ref = GeometryBatch.from_list([geos[7], geos[2], geos[5]])
+    for name in ("h", "reg_off", "a", "d", "nmk", "n_modes", "flag_off", "flags", "NT"):
+        assert np.array_equal(getattr(sub, name), getattr(ref, name)), name
+    c = gb.costs(64)
+    assert np.all(c > 0) and np.allclose(c, [geometry_cost(g, 64) for g in geos])
+    single = GeometryBatch.from_list([ofb.FlatGeometry(50.0, [1.0, 2.0], [5.0, 2.0], [16] * 3)] * 3)      # all R == 1: vectorised flag path
+    assert np.array_equal(single.flags.reshape(3, 3), [[1, 1, 0]] * 3)
