@@ -122,7 +122,9 @@ __device__ void cta_gemm_dmma(const double* __restrict__ A, int lda, const doubl
     const int mb = (Mm + 7) >> 3, nb = (Nn + 7) >> 3;
     const int tm = (mb + 7) / 8, tn = (nb + 15) / 16;     // number of CTA tiles per dimension
     for (int ti = 0; ti < tm; ++ti) {
-        const int bm0 = (int)((long)ti * mb / tm), bm1 = (int)((long)(ti + 1) * mb / tm);   // block range of this tile (<= 8)
+        // full 8-block row tiles and one remainder tile: with a triangular A the contraction of a tile starts at its FIRST row,
+        // so whole tiles (rows 0, 64, 128, ...) skip more chunks than an even split and their warp tiles are full 4 x 4
+        const int bm0 = tri >= 0 ? ti * 8 : (int)((long)ti * mb / tm), bm1 = tri >= 0 ? min(mb, bm0 + 8) : (int)((long)(ti + 1) * mb / tm);
         for (int tj = 0; tj < tn; ++tj) {
             const int bn0 = (int)((long)tj * nb / tn), bn1 = (int)((long)(tj + 1) * nb / tn);   // <= 16 blocks
             if (lower_only && (bm1 * 8 <= bn0 * 8)) continue;                // whole tile above the diagonal
