@@ -1622,6 +1622,37 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
 // Morrison closure and coefficients.  No CTA barriers, no HBM round trip between the stages: the design-sweep workload
 // (10^5 geometries x 64 omega at 16 modes per region) and the mini_bicylinder replica batch spend ~40 ns of SM time per
 // system here instead of a 256-thread CTA with 64 x 128 DMMA tiles per 16 x 16 system.
+// Per-system scalars of the one-warp kernel, one THREAD per (geometry, omega): the exterior-region exponentials, the complex
+// diagonal entry of the propagating mode (Bessel J/Y of m0 a_M), the Hankel phase and the constants of the force formula.
+// In k_freq_small these were evaluated by one lane while 31 waited (about a fifth of its instruction stream); here they run
+// at full lane occupancy.  rec[8] per system: tail, sinh(m0 L), Re D_0, Im D_0, arg H0(m0 a), omega(m0), force numerator
+// ((2 c rho) g^2), force denominator (omega m0) - the same operation order as excitation_force().
+constexpr int kSysRec = 8;
+__global__ void k_sys_pre(const void* blob, void* ws, int n_sys) {
+    DevView v = make_view(blob, ws);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_sys) return;
+    const int F = v.hdr->n_freq;
+    const int gi = t / F, f = t - gi * F;
+    const GeomDesc gd = v.geom[gi];
+    const Geom g = geom_of(v, gd);
+    const RootSet rs = v.sets[gd.root_set];
+    const double m0 = v.roots[rs.off + f];
+    const double* mk = v.roots + rs.off + F + (int64_t)f * rs.K;
+    Exterior e;
+    make_exterior(g, m0, e);
+    const cplx dg = ext_diag(0, g, e, mk);
+    double* rec = v.sysbuf + (int64_t)(gd.out_sys + f) * kSysRec;
+    rec[0] = e.tail; rec[1] = e.sinh_m0L; rec[2] = dg.re; rec[3] = dg.im;
+    rec[4] = e.inf_m0 ? 0.0 : hankel0_angle(m0 * g.a[g.M - 1]);
+    const double om = omega_of_m0(m0, g.h);
+    rec[5] = om;
+    const double T = tanh(m0 * g.h);
+    const double c = T + m0 * g.h * (1.0 - T * T);
+    rec[6] = 2.0 * c * kRhoDefault * (kG * kG);
+    rec[7] = om * m0;
+}
+
 constexpr int kSmallMax = 16, kSmallMaxR = 4, kSmallWarps = 4;
 constexpr int kSmallLdA = kSmallMax + 2 * kSmallMaxR + 1;   // 25: odd stride, conflict-free column reads
 struct SmallWs {
@@ -1673,7 +1704,13 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         const double* LA = gs + gs_base_doubles(N, R);
         const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
         __syncwarp();
-        if (lane == 0) { make_exterior(g, m0, S.ex); S.fail = 0; }
+        const double* rec = v.sysbuf + (int64_t)(gd.out_sys + f) * kSysRec;       // k_sys_pre
+        if (lane == 0) {
+            S.ex.m0 = m0; S.ex.h = g.h; S.ex.m0h = m0 * g.h;
+            S.ex.inf_m0 = isinf(m0); S.ex.lowbranch = S.ex.m0h < kM0HThresh;
+            S.ex.tail = rec[0]; S.ex.sinh_m0L = rec[1];
+            S.fail = 0;
+        }
         // the geometry's operand block into shared memory (coalesced, one latency): LA (factorised H) or HT
         const int rows_out = (lmode ? hrank : N) + 2 * R;
         {
@@ -1742,11 +1779,8 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
                 S.Imk[kk][kp] = imk(lmode ? perm[kk] : kk, (kp == K - 1) ? 0 : kp + 1, g, S.ex, mk, Nk);
             }
         }
-        if (lane < K) {
-            const cplx dg = ext_diag((lane == K - 1) ? 0 : lane + 1, g, S.ex, mk);
-            S.ext[lane] = dg.re;
-            if (lane == K - 1) S.beta = dg.im;
-        }
+        if (lane < K - 1) S.ext[lane] = ext_diag(lane + 1, g, S.ex, mk).re;       // evanescent modes: K1e / K0e ratios
+        else if (lane == K - 1) { S.ext[lane] = rec[2]; S.beta = rec[3]; }        // propagating mode: complex, from k_sys_pre
         __syncwarp();
         // 2. [-r_i ; q_j ; W] (factorised H) or [T ; -r_i ; q_j] (H itself): out[m][n] = sum_k A[k][m] Imk[k][n]
         const int nrow_t = lmode ? hrank : N;                 // rows of T / W
@@ -1814,15 +1848,15 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
             const double cre = 2.0 * kPi * ((s0[j * R + i] + (qw - beta * xei * qz)) + phi[j]);
             const double cim = 2.0 * kPi * (beta * xer * qz);
             double am = cre * v.hdr->rho;
-            double dpv = S.ex.inf_m0 ? 0.0 : cim * omega_of_m0(m0, g.h) * v.hdr->rho;
+            double dpv = S.ex.inf_m0 ? 0.0 : cim * rec[5] * v.hdr->rho;
             if (status) { am = NAN; dpv = NAN; }
             const int64_t o = gd.out_rr + ((int64_t)f * R + j) * R + i;
             out.am[o] = am;
             out.dp[o] = dpv;
             if (i == j) {
                 const int64_t o1 = gd.out_r + (int64_t)f * R + j;
-                double ph = S.ex.inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xei, xer) - hankel0_angle(m0 * g.a[M - 1]);
-                double fo = excitation_force(dpv, m0, g.h, kRhoDefault);
+                double ph = S.ex.inf_m0 ? -(kPi / 2.0) : -(kPi / 2.0) + atan2(xei, xer) - rec[4];
+                double fo = sqrt((rec[6] * dpv) / rec[7]);            // excitation_force(), constants from k_sys_pre
                 if (status) { ph = NAN; fo = NAN; }
                 out.force[o1] = fo;
                 out.phase[o1] = ph;
@@ -2448,7 +2482,9 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     else
         slots_bytes = 8 * (size_t)(H.slot_doubles_dense * P->n_slots_work);
     H.ws_slots = w; w = align_up(w + slots_bytes, 256);
-    H.ws_sysbuf = w; w = align_up(w + (b->algo == MEEMB200_ALGO_SCHUR ? 8 * (size_t)(sys_stride * P->wave_items) : 0), 256);
+    size_t sysbuf_bytes = b->algo == MEEMB200_ALGO_SCHUR ? 8 * (size_t)(sys_stride * P->wave_items) : 0;
+    if (P->use_small) sysbuf_bytes = std::max(sysbuf_bytes, 8 * (size_t)kSysRec * (size_t)n_sys);      // k_sys_pre records
+    H.ws_sysbuf = w; w = align_up(w + sysbuf_bytes, 256);
     P->blob.assign(blob_bytes, 0);
     unsigned char* bp = P->blob.data();
     memcpy(bp, &H, sizeof(H));
@@ -2466,7 +2502,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->info.n_rr = n_rr; P->info.n_r = n_r; P->info.n_sys = n_sys; P->info.n_x = n_x; P->info.n_c = n_c;
     P->info.geom_kernel = !schur ? -1 : P->use_coop2 ? 5 : P->use_coop ? 1 : P->band_variant >= 0 ? 2 + P->band_variant : 0;
     P->info.freq_kernel = !schur ? 3 : b->algo == MEEMB200_ALGO_SCHUR_LU ? 2 : P->use_small ? 1 : 0;
-    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 7 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
+    P->info.n_launches = b->algo == MEEMB200_ALGO_SCHUR ? (P->use_small ? 8 : 6 + 2 * P->n_waves) : b->algo == MEEMB200_ALGO_SCHUR_LU ? 5 : 4;
     P->solve_grid = 0;
     P->info.flops = flops;
     *out = P;
@@ -2570,6 +2606,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
         int* wave_counters = reinterpret_cast<int*>(static_cast<char*>(ws) + h->ws_counters + 256);
         const int64_t n_sys = P->info.n_sys;
         const int grid = (int)std::min<int64_t>((n_sys + kSmallWarps - 1) / kSmallWarps, P->solve_grid);
+        k_sys_pre<<<(unsigned)((n_sys + 127) / 128), 128, 0, s>>>(in, ws, (int)n_sys);
         k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters, P->gemm_flags >> 8);
         cudaEventRecord(P->ev[3], s);
         cudaEventRecord(P->ev[4], s);

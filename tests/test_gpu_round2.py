@@ -458,3 +458,31 @@ def test_cooperative_static_unequal_modes_and_many_regions(ofb, monkeypatch):
         res = plan.run()[0]
         assert np.all(res["status"] == 0)
         _check(res, mo.run_sweep(mo.FlatGeometry(*c[:4]), om, c[4], c[5]))
+
+
+def test_geometry_batch_and_stacked_download(ofb):
+    """Packed GeometryBatch (design-sweep input) through BatchPlan / ShardedPlan: same bits as the list-of-FlatGeometry path,
+    stacked [G, F, R, R] outputs without a per-geometry loop."""
+    import bench
+    from openflash_b200.distributed import ShardedPlan
+    gs = bench.c4_geometries(300)
+    om = np.linspace(0.3, 2.5, 6)
+    geos = [ofb.FlatGeometry.from_body_map(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"]) for g in gs]
+    ref = ofb.solve_batch(geos, om)
+    gb = ofb.GeometryBatch.from_dicts(gs)
+    plan = ofb.BatchPlan(gb, om)
+    plan.upload()
+    plan.solve()
+    st = plan.download_stacked(copy=True)
+    sp = ShardedPlan(gb, om)                       # world size 1: the product's multi-GPU entry degenerates to one BatchPlan
+    sp.upload()
+    sp.solve()
+    st2 = sp.download_stacked()
+    assert st["added_mass"].shape == (300, 6, 1, 1)
+    for gi, r in enumerate(ref):
+        for v in ("added_mass", "damping", "excitation_force", "excitation_phase", "m0", "status"):
+            assert np.array_equal(st[v][gi], r[v]), v
+            assert np.array_equal(st2[v][gi], r[v]), v
+    sub = ofb.solve_batch(gb.take([5, 200, 77]), om)
+    for k, gi in enumerate([5, 200, 77]):
+        assert np.array_equal(sub[k]["added_mass"], ref[gi]["added_mass"])
