@@ -1654,6 +1654,10 @@ __global__ void k_sys_pre(const void* blob, void* ws, int n_sys) {
 }
 
 constexpr int kSmallMax = 16, kSmallMaxR = 4, kSmallWarps = 4;
+// e / d for the small index ranges of the one-warp kernel (e < 1024, d <= 32) by a float multiply: the quotient's fraction
+// (r + 1/2) / d stays >= 1/64 away from an integer, far beyond the float rounding error, so the floor is exact and the
+// ~20-instruction integer division disappears from the inner loops.
+__device__ __forceinline__ int fdiv_small(int e, float rcp) { return (int)(((float)e + 0.5f) * rcp); }
 constexpr int kSmallLdA = kSmallMax + 2 * kSmallMaxR + 1;   // 25: odd stride, conflict-free column reads
 struct SmallWs {
     union {                                     // the geometry's operand block (steps 1-2), then the Cholesky block (3-4)
@@ -1713,10 +1717,11 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         }
         // the geometry's operand block into shared memory (coalesced, one latency): LA (factorised H) or HT
         const int rows_out = (lmode ? hrank : N) + 2 * R;
+        const float rl_ldn = 1.0f / (float)ldn, rl_k = 1.0f / (float)K, rl_k1 = 1.0f / (float)max(K - 1, 1);
         {
             const double* Ag = lmode ? LA : HT;
             for (int e = lane; e < N * ldn; e += 32) {
-                const int k = e / ldn, m = e - k * ldn;
+                const int k = fdiv_small(e, rl_ldn), m = e - k * ldn;
                 if (m < rows_out) S.A[k][m] = Ag[e];
             }
         }
@@ -1749,7 +1754,7 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
                 else S.Imk[row0][e - N] = imk(0, e - N + 1, g, S.ex, mk, Nk);
             }
             for (int e = lane; e < N * (K - 1); e += 32) {
-                const int n = e / (K - 1), kp = e - n * (K - 1);
+                const int n = fdiv_small(e, rl_k1), kp = e - n * (K - 1);
                 if (n == row0) continue;
                 const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
                 const double mv = tmk[kp];
@@ -1785,7 +1790,7 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         // 2. [-r_i ; q_j ; W] (factorised H) or [T ; -r_i ; q_j] (H itself): out[m][n] = sum_k A[k][m] Imk[k][n]
         const int nrow_t = lmode ? hrank : N;                 // rows of T / W
         for (int e = lane; e < rows_out * K; e += 32) {
-            const int m = e / K, n = e - m * K;
+            const int m = fdiv_small(e, rl_k), n = e - m * K;
             double acc = 0.0;
             for (int k = 0; k < N; ++k) acc = fma(S.A[k][m], S.Imk[k][n], acc);
             int a = -1, trow = -1;                            // destination: aug row a (sign) or T row
@@ -1796,16 +1801,21 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         }
         __syncwarp();
         // 3. P = A2^T T - Re(D), lower triangle, identity-padded to 16 x 16 in warp_chol16's layout
+        // padding first (upper triangle of the K x K block: 0, rows >= K: identity), then the K (K + 1) / 2 lower entries dealt
+        // to the lanes as a packed triangle, so that no lane idles on an upper-triangle slot
         for (int e = lane; e < kCholNB * kCholNB; e += 32) {
             const int m = e >> 4, n = e & 15;
-            double val = (m == n) ? 1.0 : 0.0;
-            if (m < K && n <= m) {
-                double acc = 0.0;
-                if (lmode) for (int k = 0; k < nrow_t; ++k) acc = fma(S.T[k][m], S.T[k][n], acc);
-                else for (int k = 0; k < N; ++k) acc = fma(S.Imk[k][m], S.T[k][n], acc);
-                val = (m == n) ? acc - S.ext[m] : acc;
-            } else if (m < K) val = 0.0;
-            S.Dg[m * (kCholNB + 1) + n] = val;
+            if (!(m < K && n <= m)) S.Dg[m * (kCholNB + 1) + n] = (m >= K && m == n) ? 1.0 : 0.0;
+        }
+        for (int e = lane; e < K * (K + 1) / 2; e += 32) {
+            int m = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+            if (m * (m + 1) / 2 > e) --m;                      // guard the float square root at the row boundaries
+            if ((m + 1) * (m + 2) / 2 <= e) ++m;
+            const int n = e - m * (m + 1) / 2;
+            double acc = 0.0;
+            if (lmode) for (int k = 0; k < nrow_t; ++k) acc = fma(S.T[k][m], S.T[k][n], acc);
+            else for (int k = 0; k < N; ++k) acc = fma(S.Imk[k][m], S.T[k][n], acc);
+            S.Dg[m * (kCholNB + 1) + n] = (m == n) ? acc - S.ext[m] : acc;
         }
         __syncwarp();
         // 4. P = L L^T and L^{-1} in one warp
