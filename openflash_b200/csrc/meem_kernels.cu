@@ -1792,7 +1792,8 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         for (int e = lane; e < rows_out * K; e += 32) {
             const int m = fdiv_small(e, rl_k), n = e - m * K;
             double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc = fma(S.A[k][m], S.Imk[k][n], acc);
+            // factorised form: column 2R + j of LA is column j of the lower-trapezoidal factor, zero above row j
+            for (int k = (lmode && m >= 2 * R) ? m - 2 * R : 0; k < N; ++k) acc = fma(S.A[k][m], S.Imk[k][n], acc);
             int a = -1, trow = -1;                            // destination: aug row a (sign) or T row
             if (lmode) { if (m < 2 * R) a = m; else trow = m - 2 * R; }
             else { if (m < N) trow = m; else a = m - N; }
