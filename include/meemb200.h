@@ -194,6 +194,10 @@ int meemb200_last_timing(meemb200_plan* plan, float ms[5]);
  * Synchronises the stream.  Measurement only. */
 int meemb200_phase_profile(meemb200_plan* plan, const void* d_workspace, double cycles[16], void* stream);
 
+/* Test support: report every n-th system of the following solves as a failed Cholesky, so that it is re-solved by the
+ * pivoted-LU kernel (the fallback of MEEMB200_ALGO_SCHUR, unreachable with physical inputs).  n = 0: off (default). */
+int meemb200_plan_set_test_hook(meemb200_plan* plan, int32_t flag_every);
+
 /* Host-side view of two device layouts (pure integer functions, no device needed; used by the CPU tests):
  * kind 0: out[r] = offset (doubles) of row r of the packed lower-triangular system matrix for r = 0..n, out[n+1] = padded
  *         size of the K = n triangle;

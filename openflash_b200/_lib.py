@@ -53,7 +53,7 @@ _lib = None
 EXPORTS = [
     "meemb200_version", "meemb200_last_error", "meemb200_create", "meemb200_destroy", "meemb200_sm_count",
     "meemb200_plan_create", "meemb200_plan_destroy", "meemb200_plan_info", "meemb200_plan_blob",
-    "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_solve", "meemb200_solve_host",
+    "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_plan_set_test_hook", "meemb200_solve", "meemb200_solve_host",
     "meemb200_assemble", "meemb200_imk_table", "meemb200_coefficients", "meemb200_fields", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
     "meemb200_debug_layout",
 ]
@@ -82,6 +82,7 @@ def load():
     lib.meemb200_plan_blob.restype = vp
     lib.meemb200_plan_offsets.argtypes = [vp, C.c_int32, C.POINTER(C.c_int64)]
     lib.meemb200_plan_set_freq.argtypes = [vp, vp]
+    lib.meemb200_plan_set_test_hook.argtypes = [vp, C.c_int32]
     lib.meemb200_solve.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(MeemOutputs), vp]
     lib.meemb200_solve_host.argtypes = [vp, C.POINTER(MeemOutputs), vp]
     lib.meemb200_assemble.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp, vp, vp]

@@ -355,6 +355,10 @@ class BatchPlan:
         self._refresh_host_blob()
         self._uploaded = False
 
+    def set_test_hook(self, flag_every: int):
+        """Test support: every n-th system is reported as a failed Cholesky and re-solved by the pivoted LU (0 = off)."""
+        _lib.check(self.lib.meemb200_plan_set_test_hook(self.plan, int(flag_every)))
+
     def upload(self):
         """ONE host->device copy of the packed inputs (pinned memory, current stream)."""
         self.d_blob.copy_(self.h_blob, non_blocking=True)

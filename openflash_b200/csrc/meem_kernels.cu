@@ -2377,10 +2377,6 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0);
-    if (const char* ev = getenv("MEEMB200_TEST_FLAG_EVERY")) {     // tests: every n-th system is treated as a failed Cholesky
-        const int n = atoi(ev);
-        if (n > 0 && n < (1 << 20)) P->gemm_flags |= n << 8;
-    }
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
@@ -2539,6 +2535,13 @@ extern "C" int meemb200_plan_offsets(const meemb200_plan* p, int32_t g, int64_t 
     out[6] = gd.out_c; out[7] = gd.R;
     return MEEMB200_OK;
 }
+// Test support (no reference counterpart): every n-th system of the next solves is reported as a failed Cholesky, which sends
+// it down the pivoted-LU re-solve (k_freq_lu) - the only way to reach that path with physical inputs.  n = 0 switches it off.
+extern "C" int meemb200_plan_set_test_hook(meemb200_plan* p, int32_t flag_every) {
+    if (!p || flag_every < 0 || flag_every >= (1 << 20)) return fail(MEEMB200_EINVAL, "bad argument");
+    p->gemm_flags = (p->gemm_flags & 0xff) | (flag_every << 8);
+    return MEEMB200_OK;
+}
 extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
     if (!p || !freq) return fail(MEEMB200_EINVAL, "NULL argument");
     const BlobHeader* h = p->hdr();
@@ -2627,7 +2630,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
         e = cudaFuncSetAttribute(k_freq_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
         if (e != cudaSuccess) return e;
         typedef void (*solve_fn)(const void*, void*, OutPtrs, int, int, int*, int);
-        static const solve_fn solve_k[4] = {k_freq_solve<128, 5, false>, k_freq_solve<128, 5, true>, k_freq_solve<256, 2, true>,
+        static const solve_fn solve_k[4] = {k_freq_solve<128, 4, false>, k_freq_solve<128, 5, true>, k_freq_solve<256, 2, true>,
                                             k_freq_solve<512, 1, true>};
         static const int solve_thr[4] = {128, 128, 256, 512};
         const solve_fn ksolve = solve_k[P->solve_variant];

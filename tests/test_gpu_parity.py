@@ -271,7 +271,7 @@ def test_schur_kernel_variants_vs_reference(ofb, monkeypatch, name, env):
 @pytest.mark.parametrize("small", [False, True], ids=["k_freq_solve", "k_freq_small"])
 def test_failed_cholesky_systems_are_resolved_by_lu(ofb, monkeypatch, small):
     """A system whose Cholesky reports a non-positive pivot (status bit 2) is re-solved by the pivoted LU of the unreduced
-    K x K system (k_freq_lu, only_flagged pass) and leaves with status 0.  MEEMB200_TEST_FLAG_EVERY=3 makes the solve kernels
+    K x K system (k_freq_lu, only_flagged pass) and leaves with status 0.  meemb200_plan_set_test_hook(plan, 3) makes the solve kernels
     report every third system as failed: those systems must come back within the parity bar (and not bit-identical to the
     Cholesky answer - the re-solve really ran), the others bit-identical to the unhooked run.  The scan for flagged systems
     covers more systems than one CTA pass (blockDim x gridDim), so its chunked loop wraps."""
@@ -286,8 +286,9 @@ def test_failed_cholesky_systems_are_resolved_by_lu(ofb, monkeypatch, small):
     # wrap-around of the scan is exercised with the small systems (600 omega x 160 geometries = 96 000 systems)
     geos = [geo] * (160 if small else 2)
     plain = ofb.solve_batch(geos, om)
-    monkeypatch.setenv("MEEMB200_TEST_FLAG_EVERY", "3")
-    hooked = ofb.solve_batch(geos, om)
+    hplan = ofb.BatchPlan(geos, om)
+    hplan.set_test_hook(3)
+    hooked = hplan.run()
     ref = mo.run_sweep(mo.FlatGeometry(h, a, d, NMK), om, bm, modes)
     F = len(om)
     differs = 0
