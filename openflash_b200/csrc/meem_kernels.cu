@@ -2391,12 +2391,20 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         delete P;
         return fail(MEEMB200_EINVAL, "system too large for the shared-memory LU panels");
     }
-    {   // cooperative geometry stage when it beats one CTA per geometry (cost model from measured timings:
-        // single CTA ~6e-8 p^3 ms per geometry, cooperative ~1.5e-3 p ms per geometry)
+    {   // cooperative geometry stage when it beats one CTA per geometry.  Cost model from measured timings (ms; v16,
+        // tools/experiments/size_scan.py): one CTA per geometry takes ~1.2e-5 p^2 per wave by window elimination (~6e-8 p^3 by
+        // the dense LU of the X path); the cooperative kernels process the geometries one after another at ~0.08 + 7.8e-4 p each
+        // (static-pivot windows) or ~1.5e-3 p each (dense LU).
         const double waves = std::ceil((double)G / ctx->sm_count);
+        const double pp = (double)max_p;
         P->smem_coop = coop_smem_bytes(max_p);
-        const bool few_large = (double)G * 1.5e-3 * max_p < waves * 6e-8 * (double)max_p * max_p * max_p;
-        bool want_coop = schur && few_large;
+        P->coop2_wrows = coop2_wrows; P->coop2_wcols = coop2_wcols;
+        P->smem_coop2 = coop2_smem_bytes(coop2_wrows, max_N);
+        const bool coop2_ok = schur && all_case1 && !b->want_x && P->smem_coop2 + 8192 <= limit && !getenv("MEEMB200_NO_COOP2");
+        const bool band_ok = schur && !b->want_x && !getenv("MEEMB200_NO_BAND");
+        const double t_one = band_ok ? 1.2e-5 * pp * pp : 6e-8 * pp * pp * pp;
+        const double t_coop = coop2_ok ? 0.08 + 7.8e-4 * pp : 1.5e-3 * pp;
+        bool want_coop = schur && (double)G * t_coop < waves * t_one;
         if (getenv("MEEMB200_NO_COOP")) want_coop = false;
         if (getenv("MEEMB200_FORCE_COOP")) want_coop = schur;                                      // tests
         P->use_coop = want_coop && P->smem_coop + 8192 <= limit;
@@ -2404,9 +2412,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         if (P->use_coop)
             for (int gi = 0; gi < G; ++gi) slot_geom = std::max<int64_t>(slot_geom, coop_slot_doubles(P->geoms[gi].p, P->geoms[gi].N, P->geoms[gi].R));
         // static-pivot window variant: depths decreasing outwards everywhere (the C1 blocks then sit on diagonal pivot blocks), no X
-        P->coop2_wrows = coop2_wrows; P->coop2_wcols = coop2_wcols;
-        P->smem_coop2 = coop2_smem_bytes(coop2_wrows, max_N);
-        P->use_coop2 = want_coop && all_case1 && !b->want_x && P->smem_coop2 + 8192 <= limit && !getenv("MEEMB200_NO_COOP2");
+        P->use_coop2 = want_coop && coop2_ok;
         if (P->use_coop2) { P->use_coop = true; slot_geom = coop2_slot_doubles(coop2_wrows, coop2_wcols); }
     }
     P->band_variant = -1; P->band_wrows = band_wrows; P->band_wcols = band_wcols; P->band_grid = 0; P->smem_band = 0;
