@@ -73,6 +73,13 @@ def workload(name, rank, world):
         n = 12500
         gs = c4_geometries(n * world)[rank * n:(rank + 1) * n]
         return gs, np.linspace(0.3, 2.5, 64), "random N-cylinder (M=2..8, 16 modes/region) design sweep, 12500 geometries x 64 omega per GPU"
+    if name == "convergence_sweep":     # configs[4] / C5: mode-count convergence, 12 mode counts x 2 geometries x 8 omega
+        ns = [10, 15, 20, 30, 40, 50, 75, 100, 150, 200, 300, 400]
+        gs = [dict(h=1.001, a=[0.5, 1.0], d=[0.5, 0.25], NMK=[n] * 3, body_map=[0, 0], modes=[0]) for n in ns]
+        gs += [dict(h=20.0, a=[5.0, 10.0, 15.0], d=[15.0, 10.0, 5.0], NMK=[n] * 4, body_map=[0, 0, 0], modes=[0]) for n in ns]
+        gs = gs[rank::world] if world > 1 else gs
+        return gs, np.linspace(0.5, 3.0, 8), ("mode-count convergence sweep 10..400 modes/region on small_bicylinder and small_tricylinder, 8 omega "
+                                               "(the reference's exp() overflows at the largest mode counts: those systems are NaN there and here)")
     if name == "sweep_1e6":             # north star: 10^6 systems = first 15 625 C4 geometries x 64 omega, FIXED total
         return c4_geometries(15625), np.linspace(0.3, 2.5, 64), "first 15625 C4 geometries x 64 omega = 10^6 systems in total (strong scaling)"
     raise SystemExit(f"unknown workload {name}")
@@ -176,7 +183,8 @@ def run_cpu(kind, geoms, omegas, target_systems, pool, cores, min_seconds=0.0, m
 def cpu_target(name, kind):
     """Systems per timed pass.  The reference rebuilds its per-geometry cache in every task (meem_engine.py:100-305:
     0.3 s for big_tricylinder), exactly as a user's run_and_store_results call does."""
-    t = {"big_tricylinder": 512, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64, "sweep_1e6": 64}[name]
+    t = {"big_tricylinder": 512, "small_tricylinder": 256, "mini_bicylinder": 2048, "geometry_sweep": 64, "sweep_1e6": 64,
+         "convergence_sweep": 48}[name]
     return t if kind == "port" else max(t // 4, 32)
 
 
@@ -507,7 +515,7 @@ def main():
             e2e["solve_host"] = {"ms_per_call": ms, "value": total_sys / (ms * 1e-3),
                                  "api": "meemb200_solve_host via raw ctypes (INTEGRATION.md stub): H2D + kernels + D2H into caller-owned host arrays"}
             wl = {}
-            for name in ("mini_bicylinder", "small_tricylinder", "geometry_sweep"):
+            for name in ("mini_bicylinder", "small_tricylinder", "geometry_sweep", "convergence_sweep"):
                 if name == args.workload:
                     continue
                 r2 = Runner(ofb, name, 1, 0, dev, "schur", flush)
