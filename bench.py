@@ -322,7 +322,9 @@ class Runner:
             t0 = time.perf_counter()
             self.sp.upload()
             self.sp.solve()
-            packed = self.sp.download_packed()          # every output of every rank in host memory (pinned), one copy
+            # every output of this rank's shard into pinned host memory, one copy per rank (N > 1: all PCIe links in parallel;
+            # the gathered copy of every shard stays on every GPU)
+            packed = self.sp.download_local_packed()
             checksum = int(packed[::4096].sum()) if packed is not None else 0      # the host really reads the result buffer
             torch.cuda.synchronize()
             ms += 1e3 * (time.perf_counter() - t0)
@@ -485,7 +487,7 @@ def main():
                               "gather_ms": round(sw_ms / ksw - max(per_rank), 4),
                               "gather": "NCCL all_gather of the packed output buffers (the path's only exchange): every rank ends with every result",
                               "e2e": {"value": sw.total_sys * 2 / (sw_e2e_ms * 1e-3), "ms_per_step": sw_e2e_ms / 2,
-                                      "includes": "H2D inputs, kernels, all_gather, one pinned D2H of every rank's outputs on every rank"},
+                                      "includes": "H2D inputs, kernels, all_gather, one pinned D2H of each rank's own shard (all PCIe links in parallel)"},
                               "plan_ms_once": round(sw.plan_ms, 1), "workload": sw.desc, "failed_systems": int(failed)}
         if world > 1:       # the same sweep with the results delivered to rank 0 only (NCCL gather: serialised receives, not faster)
             sw2 = Runner(ofb, "sweep_1e6", world, rank, dev, "schur", flush, gather="root")
@@ -507,9 +509,9 @@ def main():
         roofline["phase_share"] = ({k: (round(v, 4) if isinstance(v, float) else v) for k, v in plan.phase_profile().items()}
                                    if args.algo == "schur" else None)
         roofline["dense_equivalent_tflops"] = value * (8.0 / 3.0 * run.flat[0].size ** 3 + 8.0 * run.flat[0].size ** 2 * run.flat[0].R) / 1e12
-        e2e = {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": plan.h2d_bytes, "d2h_bytes_per_step": int(plan.d2h_bytes) * world,
+        e2e = {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": plan.h2d_bytes * world, "d2h_bytes_per_step": int(plan.d2h_bytes) * world,
                "ms_per_step": e2e_ms / e2e_steps,
-               "api": "ShardedPlan.upload + solve + download_packed (pinned H2D of the packed inputs, kernels, gather, one pinned D2H of every output)"}
+               "api": "ShardedPlan.upload + solve + download_local_packed on every rank (pinned H2D of the packed inputs, kernels, all_gather, one pinned D2H of the rank's own shard)"}
         if world == 1 and not args.no_extra and args.algo == "schur":
             ms = solve_host_ms(ofb, geoms, omegas)
             e2e["solve_host"] = {"ms_per_call": ms, "value": total_sys / (ms * 1e-3),

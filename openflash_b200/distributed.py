@@ -160,6 +160,16 @@ class ShardedPlan:
             self.torch.cuda.current_stream(self.gathered.device).synchronize()
         return self.h_gathered.numpy()
 
+    def download_local_packed(self):
+        """ONE device->host copy of THIS rank's packed outputs (its shard only) into its pinned buffer: with one process
+        per GPU the shards reach host memory over all PCIe links in parallel, instead of every rank pulling all 8 shards
+        through its own link.  Layout: ``layouts[rank]``; None for a rank without work."""
+        if self.local is None:
+            return None
+        self.local.h_out.copy_(self.local.d_out, non_blocking=True)
+        self.torch.cuda.current_stream(self.local.device).synchronize()
+        return self.local.h_out.numpy()
+
     def download(self):
         """Per-geometry result dicts in the caller's geometry order, frequencies re-joined (every rank holds them all)."""
         from .batch import split_outputs, unpack_outputs
