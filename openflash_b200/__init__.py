@@ -10,3 +10,4 @@ from .results import Results  # noqa: F401
 from .batch import (BatchPlan, FlatGeometry, GeometryBatch, solve_batch, device_roots, device_bessel, fp64_peak,  # noqa: F401
                     ALGO_SCHUR, ALGO_DENSE, ALGO_SCHUR_LU, ROOTS_REFERENCE, ROOTS_CONVERGED, FREQ_OMEGA, FREQ_M0)
 from .meem_engine import MEEMEngine, flatten_problem  # noqa: F401
+from .distributed import ShardedPlan, solve_batch_distributed  # noqa: F401
