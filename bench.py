@@ -530,6 +530,20 @@ def main():
                             "failed_systems": int(sum(np.count_nonzero(r["status"]) for r in r2.res))}
                 del r2
             extra["workloads"] = wl
+            # BASELINE.json configs[0] exactly as the reference's CPU artifact: ONE problem, ONE frequency, through the class API
+            geo = ofb.BasicRegionGeometry.from_vectors(a=np.array([0.125, 0.25]), d=np.array([0.25, 0.125]), h=1.001, NMK=[10] * 3,
+                                                       body_map=[0, 0], heaving_map=[True])
+            prob = ofb.MEEMProblem(geo)
+            prob.set_frequencies(np.array([float(np.sqrt(np.tanh(1.001) * 9.81))]))
+            eng = ofb.MEEMEngine([prob], device=local_rank)
+            lat = []
+            for _ in range(25):
+                t0 = time.perf_counter()
+                ds = eng.run_and_store_results(0).dataset
+                lat.append(1e3 * (time.perf_counter() - t0))
+            extra["latency"] = {"mini_bicylinder_single_frequency_ms": float(np.median(lat[5:])),
+                                "api": "MEEMEngine.run_and_store_results(0): plan + H2D + kernels + D2H + Results packaging, median of 20 calls",
+                                "added_mass": float(np.asarray(ds["added_mass"].values)[0, 0, 0])}
         cpu = None
         if not args.no_cpu and world == 1:
             import multiprocessing as mp
