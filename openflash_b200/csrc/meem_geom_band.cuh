@@ -52,9 +52,38 @@ MEEM_HDX void band_dims(const Geom& g, const Layout& L, int R, BandDims& D) {
 // All threads of the CTA must call.  W: window buffer [wrows][ld] (shared or global), side: hand-over buffer,
 // lu_smem: lu_smem_bytes<double, NB, CHUNK>(wrows).  On return, with n = unknowns of the last region and N = nmk[M-1]:
 // rows [0, n) x cols [n, n+N+R) = rows of the last region of [G | y0_i]; rows [n, n+R) x the same columns = -[w_j | s0_ji].
+// Static-pivot step of a case-1 window (potential rows FIRST): the C1 block of the potential rows is the diagonal matrix
+// (h - d_bd) diag R_1n(a_bd), so its Nb columns are eliminated without a pivot search and without a panel factorisation -
+// per NB columns: multipliers W[r][k] / D1_k of the rows below and the pivot rows' other columns are staged, then one
+// rank-NB update by all warps.  Probe: tools/experiments/exp_band.py --static (<= 9e-15 incl. mixed case-1 / case-2 geometries).
+template <int NB, bool SMALL, int CHUNK>
+__device__ void band_static_step(double* W, long ld, int nrows, int ncols, int Nb, unsigned char* smem_raw) {
+    double* panel = reinterpret_cast<double*>(smem_raw);     // [NB][nrows]: multipliers of rows Nb .. nrows-1
+    double* ust = panel + (size_t)NB * nrows;                // [NB][CHUNK]
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int below = nrows - Nb;
+    for (int k0 = 0; k0 < Nb; k0 += NB) {
+        const int nbj = min(NB, Nb - k0);
+        for (int idx = tid; idx < below * nbj; idx += nthr) {
+            const int i = idx / nbj, q = idx - i * nbj;
+            panel[q * nrows + i] = W[(long)(Nb + i) * ld + k0 + q] / W[(long)(k0 + q) * ld + k0 + q];
+        }
+        for (int cc0 = Nb; cc0 < ncols; cc0 += CHUNK) {
+            const int cc1 = min(ncols, cc0 + CHUNK);
+            for (int idx = tid; idx < nbj * (cc1 - cc0); idx += nthr) {
+                const int q = idx / (cc1 - cc0), c = idx - q * (cc1 - cc0);
+                ust[q * CHUNK + c] = W[(long)(k0 + q) * ld + cc0 + c];
+            }
+            __syncthreads();
+            lu_rank_update<double, NB, SMALL, CHUNK>(W, ld, Nb, nrows, Nb, panel, nrows, cc0, cc1, ust, nbj);
+            __syncthreads();
+        }
+    }
+}
+
 template <int NB, bool SMALL, int CHUNK>
 __device__ void band_eliminate(const Geom& g, const Layout& L, const double* tab, const unsigned char* flags, int R,
-                               double* W, long ld, double* side, unsigned char* lu_smem, int* status) {
+                               double* W, long ld, double* side, unsigned char* lu_smem, int* status, bool use_static) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int M = g.M;
     int nc = 0;
@@ -63,6 +92,9 @@ __device__ void band_eliminate(const Geom& g, const Layout& L, const double* tab
         const int n0 = band_unknowns(g, bd), n1 = last ? g.nmk[M - 1] : band_unknowns(g, bd + 1);
         const int hp = L.pot_h[bd], hv = last ? 0 : L.vel_h[bd];
         const int nsearch = nc + hp + hv, nrows = nsearch + R, ncols = n0 + n1 + R;
+        // case-1 boundary (and the last one): potential rows first, their diagonal C1 block is eliminated without a search
+        const bool stat = use_static && (last || g.d[bd] > g.d[bd + 1]);
+        const int r_car = stat ? hp : 0, r_pot = stat ? 0 : nc, r_vel = nc + hp;
         for (int e = tid; e < nrows * ncols; e += nthr) {
             const int r = e / ncols, c = e - r * ncols;
             W[(long)r * ld + c] = 0.0;
@@ -72,7 +104,7 @@ __device__ void band_eliminate(const Geom& g, const Layout& L, const double* tab
             const int sw = n0 + R;
             for (int e = tid; e < (nc + R) * sw; e += nthr) {
                 const int r = e / sw, c = e - r * sw;
-                const int wr = r < nc ? r : nsearch + (r - nc);
+                const int wr = r < nc ? r_car + r : nsearch + (r - nc);
                 const int wc = c < n0 ? c : n0 + n1 + (c - n0);
                 W[(long)wr * ld + wc] = side[e];
             }
@@ -90,16 +122,22 @@ __device__ void band_eliminate(const Geom& g, const Layout& L, const double* tab
                     c_entry(g, L, tab, flags + (long)j * (M + 1), bd + 1, c < Nr ? 0 : 1, c < Nr ? c : c - Nr);
             }
         } else {
-            for (int n = tid; n < n1; n += nthr) W[(long)(nc + n) * ld + n0 + n] = 1.0;     // E
+            for (int n = tid; n < n1; n += nthr) W[(long)(r_pot + n) * ld + n0 + n] = 1.0;     // E
         }
-        fill_A_boundary<double>(g, L, tab, bd, W, ld, nc, nc + hp, L.col[bd], tid, nthr);
+        fill_A_boundary<double>(g, L, tab, bd, W, ld, r_pot, r_vel, L.col[bd], tid, nthr);
         for (int e = tid; e < R * (hp + hv); e += nthr) {
             const int i = e / (hp + hv), n = e - i * (hp + hv);
             const bool vel = n >= hp;
-            W[(long)(nc + n) * ld + n0 + n1 + i] = b_static_entry(g, L, flags + (long)i * (M + 1), bd, vel, vel ? n - hp : n);
+            W[(long)(vel ? r_vel + (n - hp) : r_pot + n) * ld + n0 + n1 + i] =
+                b_static_entry(g, L, flags + (long)i * (M + 1), bd, vel, vel ? n - hp : n);
         }
         __syncthreads();
-        lu_forward<double, NB, SMALL, CHUNK>(W, ld, nrows, n0, ncols, lu_smem, status, nsearch);
+        if (stat) {
+            band_static_step<NB, SMALL, CHUNK>(W, ld, nrows, ncols, hp, lu_smem);
+            lu_forward<double, NB, SMALL, CHUNK>(W + (long)hp * ld + hp, ld, nrows - hp, n0 - hp, ncols - hp, lu_smem, status, nsearch - hp);
+        } else {
+            lu_forward<double, NB, SMALL, CHUNK>(W, ld, nrows, n0, ncols, lu_smem, status, nsearch);
+        }
         if (last) {
             lu_backward<double, NB, SMALL, CHUNK>(W, ld, n0, n0, ncols, lu_smem, n0);
             __syncthreads();

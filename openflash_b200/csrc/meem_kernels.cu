@@ -402,7 +402,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_geom(const void* blob, void* 
 constexpr int kBandSmallChunk = 72;      // U12 staging chunk of the small variant (>= the 65 window columns of N = 16, R = 1)
 __host__ __device__ inline int band_ld(int wcols, bool smem) { return smem ? (wcols | 1) : ((wcols + 1) & ~1); }
 template <int NB, int THREADS, int MINB, bool SMALL, bool SMEMWIN, int CHUNK>
-__global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, void* ws, int wrows_max, int wcols_max, int side_alias) {
+__global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, void* ws, int wrows_max, int wcols_max, int side_alias,
+                                                             int use_static) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ Layout L;
     __shared__ int sh_item, sh_status;
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_geom_band(const void* blob, v
         const int N = gd.N, R = gd.R, M = gd.M;
         const double* tab = v.tables + gd.tab_off;
         const uint8_t* flags = v.flags + gd.flag_off;
-        band_eliminate<NB, SMALL, CHUNK>(g, L, tab, flags, R, W, ld, side, smem, &sh_status);
+        band_eliminate<NB, SMALL, CHUNK>(g, L, tab, flags, R, W, ld, side, smem, &sh_status, use_static != 0);
         // reduce to what the frequency stage needs (same store layout as k_geom)
         double* gs = v.gstore + gd.gs_off;
         double* HT = gs;
@@ -2204,6 +2205,7 @@ struct meemb200_plan {
     int band_variant;       // geometry stage by window elimination (k_geom_band): -1 off, 0 small window in shared memory (128 threads),
                             // 1 window in shared memory (256 threads), 2 window in the CTA's global slot (512 threads)
     int band_wrows, band_wcols, band_grid, band_side_alias;
+    bool band_static;       // k_geom_band eliminates the C1 block of case-1 windows on its diagonal (no pivot search); MEEMB200_NO_BAND_STATIC
     size_t smem_band;
     int64_t wave_items;     // systems per frequency-stage wave
     int n_waves, solve_grid;
@@ -2415,6 +2417,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         P->use_coop2 = want_coop && coop2_ok;
         if (P->use_coop2) { P->use_coop = true; slot_geom = coop2_slot_doubles(coop2_wrows, coop2_wcols); }
     }
+    P->band_static = !getenv("MEEMB200_NO_BAND_STATIC");
     P->band_variant = -1; P->band_wrows = band_wrows; P->band_wcols = band_wcols; P->band_grid = 0; P->smem_band = 0;
     if (schur && !b->want_x && !P->use_coop && !getenv("MEEMB200_NO_BAND")) {
         // window elimination instead of the dense p x p LU (meem_geom_band.cuh); X needs all of G and keeps the dense form
@@ -2581,7 +2584,7 @@ static cudaError_t launch_geom_coop(meemb200_plan* P, const void* in, void* ws, 
     return cudaLaunchCooperativeKernel((void*)k_geom_coop, dim3(P->ctx->sm_count), dim3(kCoopThreads), args, P->smem_coop, s);
 }
 static cudaError_t launch_geom_band(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {
-    typedef void (*band_fn)(const void*, void*, int, int, int);
+    typedef void (*band_fn)(const void*, void*, int, int, int, int);
     static const band_fn fns[3] = {k_geom_band<8, 128, 6, true, true, kBandSmallChunk>, k_geom_band<8, 256, 2, false, true, kLuChunk>,
                                    k_geom_band<8, 512, 1, false, false, kLuChunk>};
     static const int thr[3] = {128, 256, 512};
@@ -2596,7 +2599,7 @@ static cudaError_t launch_geom_band(meemb200_plan* P, const void* in, void* ws, 
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
         P->band_grid = P->band_variant == 2 ? P->n_slots_geom : (int)std::min<int64_t>(P->hdr()->n_geom, (int64_t)per_sm * P->ctx->sm_count);
     }
-    kfn<<<P->band_grid, nthr, P->smem_band, s>>>(in, ws, P->band_wrows, P->band_wcols, P->band_side_alias);
+    kfn<<<P->band_grid, nthr, P->smem_band, s>>>(in, ws, P->band_wrows, P->band_wcols, P->band_side_alias, P->band_static ? 1 : 0);
     return cudaGetLastError();
 }
 template <int NB> static cudaError_t launch_geom(meemb200_plan* P, const void* in, void* ws, cudaStream_t s) {

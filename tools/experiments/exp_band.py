@@ -23,15 +23,19 @@ from oracle import meem_oracle as mo  # noqa: E402
 warnings.simplefilter("ignore")
 
 
-def lu_window(W, npiv, nsearch):
-    """In-place partial-pivot elimination of the first npiv columns; pivot rows searched in rows < nsearch only."""
+def lu_window(W, npiv, nsearch, nstatic=0):
+    """In-place partial-pivot elimination of the first npiv columns; pivot rows searched in rows < nsearch only.
+    The first nstatic columns take the diagonal entry as pivot without a search (static pivots, k_geom_band / k_geom_coop2)."""
     for k in range(npiv):
-        q = k + int(np.argmax(np.abs(W[k:nsearch, k])))
+        q = k if k < nstatic else k + int(np.argmax(np.abs(W[k:nsearch, k])))
         if q != k:
             W[[k, q]] = W[[q, k]]
         l = W[k + 1:, k] / W[k, k]
         W[k + 1:, k + 1:] -= np.outer(l, W[k, k + 1:])
         W[k + 1:, k] = 0.0
+
+
+STATIC = False      # windows of case-1 boundaries: potential rows first, C1 block eliminated on its diagonal without a pivot search
 
 
 def band_reduce(geo, flags_list, A11, B1, cvecs):
@@ -45,19 +49,24 @@ def band_reduce(geo, flags_list, A11, B1, cvecs):
     crow = np.zeros((R, R))          # right-hand-side part of the c rows
     ccur = np.array([c[col[0]:col[0] + nun[0]] for c in cvecs]).reshape(R, nun[0])
     for bd in range(M - 1):
-        rows = list(range(pot[bd][0], pot[bd][0] + pot[bd][1])) + list(range(vel[bd][0], vel[bd][0] + vel[bd][1]))
+        prow = list(range(pot[bd][0], pot[bd][0] + pot[bd][1]))
+        vrow = list(range(vel[bd][0], vel[bd][0] + vel[bd][1]))
+        rows = prow + vrow
         n0, n1 = nun[bd], nun[bd + 1]
         nc = carried.shape[0]
+        static = STATIC and geo.dext[bd] > geo.dext[bd + 1]
         W = np.zeros((nc + len(rows) + R, n0 + n1 + R))
+        r_car, r_new = (len(prow), [0, len(prow) + nc]) if static else (0, [nc, nc + len(prow)])
         if nc:
-            W[:nc, :n0] = carried[:, :n0]
-            W[:nc, n0 + n1:] = carried[:, n0:]
-        W[nc:nc + len(rows), :n0 + n1] = A11[np.ix_(rows, range(col[bd], col[bd] + n0 + n1))]
-        W[nc:nc + len(rows), n0 + n1:] = B1[rows]
+            W[r_car:r_car + nc, :n0] = carried[:, :n0]
+            W[r_car:r_car + nc, n0 + n1:] = carried[:, n0:]
+        for rr, r0 in ((prow, r_new[0]), (vrow, r_new[1])):
+            W[r0:r0 + len(rr), :n0 + n1] = A11[np.ix_(rr, range(col[bd], col[bd] + n0 + n1))]
+            W[r0:r0 + len(rr), n0 + n1:] = B1[rr]
         W[nc + len(rows):, :n0] = ccur
         W[nc + len(rows):, n0:n0 + n1] = np.array([c[col[bd + 1]:col[bd + 1] + n1] for c in cvecs]).reshape(R, n1)
         W[nc + len(rows):, n0 + n1:] = crow
-        lu_window(W, n0, nc + len(rows))
+        lu_window(W, n0, nc + len(rows), NMK[bd] if static else 0)
         carried = W[n0:nc + len(rows), n0:].copy()
         ccur = W[nc + len(rows):, n0:n0 + n1].copy()
         crow = W[nc + len(rows):, n0 + n1:].copy()
@@ -67,15 +76,16 @@ def band_reduce(geo, flags_list, A11, B1, cvecs):
     nc = carried.shape[0]
     assert nc + len(rows) == n0
     W = np.zeros((n0 + R, n0 + N + R))
+    r_car, r_pot = (len(rows), 0) if STATIC else (0, nc)
     if nc:
-        W[:nc, :n0] = carried[:, :n0]
-        W[:nc, n0 + N:] = carried[:, n0:]
-    W[nc:n0, :n0] = A11[np.ix_(rows, range(col[bd], col[bd] + n0))]
-    W[nc:n0, n0:n0 + N] = np.eye(N)
-    W[nc:n0, n0 + N:] = B1[rows]
+        W[r_car:r_car + nc, :n0] = carried[:, :n0]
+        W[r_car:r_car + nc, n0 + N:] = carried[:, n0:]
+    W[r_pot:r_pot + len(rows), :n0] = A11[np.ix_(rows, range(col[bd], col[bd] + n0))]
+    W[r_pot:r_pot + len(rows), n0:n0 + N] = np.eye(N)
+    W[r_pot:r_pot + len(rows), n0 + N:] = B1[rows]
     W[n0:, :n0] = ccur
     W[n0:, n0 + N:] = crow
-    lu_window(W, n0, n0)
+    lu_window(W, n0, n0, NMK[bd] if STATIC else 0)
     Glast = linalg.solve_triangular(W[:n0, :n0], W[:n0, n0:])
     return Glast, -W[n0:, n0:n0 + N], -W[n0:, n0 + N:]
 
@@ -113,6 +123,10 @@ def check(name, h, a, d, NMK, region_body=None, modes=None):
 
 
 if __name__ == "__main__":
+    if "--static" in sys.argv:
+        sys.argv.remove("--static")
+        STATIC = True
+        print("static pivots for the C1 block of every case-1 window (potential rows first)")
     cases = [("mini", (1.001, [0.125, 0.25], [0.25, 0.125], [10] * 3)), ("small", (20.0, [5, 10, 15], [15, 10, 5], [50] * 4)),
              ("single", (3.0, [1.0], [0.7], [9, 11])), ("overhang", (1.001, [0.5, 1.0], [0.25, 0.5], [6, 7, 8])),
              ("config3", (1.9, [0.3, 0.5, 1.0, 1.2, 1.6], [0.5, 0.7, 0.8, 0.2, 0.5], [8, 9, 10, 11, 12, 13])),
