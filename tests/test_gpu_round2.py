@@ -33,7 +33,7 @@ def _check(out, ref, tol=1e-10):
 
 
 BAND_ENVS = [{"MEEMB200_BAND_VARIANT": "0"}, {"MEEMB200_BAND_VARIANT": "1"}, {"MEEMB200_BAND_VARIANT": "2"}, {"MEEMB200_NO_BAND": "1"},
-             {"MEEMB200_NO_COOP": "1"}]
+             {"MEEMB200_NO_COOP": "1"}, {"MEEMB200_NO_BAND_STATIC": "1"}, {"MEEMB200_NO_BAND_STATIC": "1", "MEEMB200_BAND_VARIANT": "2"}]
 _ids = lambda e: "-".join(f"{k[9:]}={v}" for k, v in e.items())  # noqa: E731
 
 
@@ -53,7 +53,7 @@ def test_window_elimination_variants_vs_reference(ofb, monkeypatch, name, env):
         _check(r, ref)
 
 
-@pytest.mark.parametrize("env", BAND_ENVS[:4], ids=_ids)
+@pytest.mark.parametrize("env", BAND_ENVS[:4] + BAND_ENVS[5:], ids=_ids)
 def test_window_elimination_heterogeneous_batch(ofb, monkeypatch, env):
     """C4 generator (mixed M = 2..8, 10 % overhanging depth orders) plus single cylinders, unequal mode counts per region and
     two radiating bodies in ONE batch: every window shape (first / interior / last, case 1 and case 2 row counts)."""
