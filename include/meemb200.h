@@ -144,6 +144,24 @@ int meemb200_solve(meemb200_plan* plan, const void* d_input, void* d_workspace, 
  * and the plan keeps the allocation for later calls (released by meemb200_plan_destroy). */
 int meemb200_solve_host(meemb200_plan* plan, const MeemOutputs* host_out, void* stream);
 
+/* Allocation-free variant of meemb200_solve.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The workspace - the scratch memory every kernel of the pipeline works in - is a file-scope
+ * `static __device__ __align__(256)` array of MEEMB200_STATIC_WS_BYTES inside the library (each GPU that loads the
+ * library holds its copy until the process exits); its device address is resolved once per device with
+ * cudaGetSymbolAddress.  The caller still passes the uploaded inputs (d_input, as for meemb200_solve) and the device
+ * output pointers.  The call itself makes no cudaMalloc / cudaFree / allocating library call; the first solve on a plan
+ * creates the plan's six timing events (cudaEventCreate, host-side handles only), as meemb200_solve does.
+ *   - plans whose MeemPlanInfo.workspace_bytes exceeds MEEMB200_STATIC_WS_BYTES are refused with MEEMB200_ENOMEM and a
+ *     message naming both sizes (nothing is enqueued): use meemb200_solve with a caller-owned workspace for those;
+ *   - ALL calls on a device share the one array, which keeps the last call's contents.  The prologue zeroes the
+ *     work-queue counters (the only part that must start at zero) on `stream`; everything else is written before it is
+ *     read.  Two calls that overlap on the GPU (different streams, or different plans / threads without ordering) RACE
+ *     on the array: order them on one stream or with events, or give the overlapping call its own workspace through
+ *     meemb200_solve. */
+#define MEEMB200_STATIC_WS_BYTES (32u << 20)
+int meemb200_solve_static_ws(meemb200_plan* plan, const void* d_input, const MeemOutputs* out, void* stream);
+
 /* Parity / debugging exports mirroring the reference's intermediate API (device pointers).
  * A: [NT][NT] complex128 row-major, b: [R][NT] complex128, c: [R][p+1] complex128 (the c vector of
  * mode j followed by sum_i heaving_j[i]*int_phi_p_i) for geometry g of the plan at frequency index f.

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(HERE, "libmeemb200.so")
 ALGO_SCHUR, ALGO_DENSE, ALGO_SCHUR_LU = 0, 1, 2
 ROOTS_REFERENCE, ROOTS_CONVERGED = 0, 1
 FREQ_OMEGA, FREQ_M0 = 0, 1
+STATIC_WS_BYTES = 32 << 20      # MEEMB200_STATIC_WS_BYTES (include/meemb200.h)
 
 
 class MeemBatch(C.Structure):
@@ -53,7 +54,7 @@ _lib = None
 EXPORTS = [
     "meemb200_version", "meemb200_last_error", "meemb200_create", "meemb200_destroy", "meemb200_sm_count",
     "meemb200_plan_create", "meemb200_plan_destroy", "meemb200_plan_info", "meemb200_plan_blob",
-    "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_plan_set_test_hook", "meemb200_solve", "meemb200_solve_host",
+    "meemb200_plan_offsets", "meemb200_plan_set_freq", "meemb200_plan_set_test_hook", "meemb200_solve", "meemb200_solve_host", "meemb200_solve_static_ws",
     "meemb200_assemble", "meemb200_imk_table", "meemb200_coefficients", "meemb200_fields", "meemb200_roots", "meemb200_bessel", "meemb200_fp64_peak", "meemb200_last_timing", "meemb200_phase_profile",
     "meemb200_debug_layout",
 ]
@@ -85,6 +86,7 @@ def load():
     lib.meemb200_plan_set_test_hook.argtypes = [vp, C.c_int32]
     lib.meemb200_solve.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(MeemOutputs), vp]
     lib.meemb200_solve_host.argtypes = [vp, C.POINTER(MeemOutputs), vp]
+    lib.meemb200_solve_static_ws.argtypes = [vp, vp, C.POINTER(MeemOutputs), vp]
     lib.meemb200_assemble.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp, vp, vp]
     lib.meemb200_imk_table.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp]
     lib.meemb200_coefficients.argtypes = [vp, vp, vp, C.c_size_t, C.c_int32, C.c_int32, vp, vp, vp]

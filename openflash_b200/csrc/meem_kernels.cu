@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <map>
+#include <mutex>
 #include <cstdlib>
 #include <cmath>
 #include <string>
@@ -2830,6 +2831,45 @@ extern "C" int meemb200_solve_host(meemb200_plan* P, const MeemOutputs* ho, void
     e = cudaStreamSynchronize(s);
     if (!rc && e != cudaSuccess) rc = fail(MEEMB200_ECUDA, std::string("solve_host: ") + cudaGetErrorString(e));
     return rc;
+}
+
+// ---- allocation-free solve: the workspace (scratch of every kernel of the pipeline) lives in the library image.
+// g_static_ws is a DEVICE symbol: in host code its name is only a handle for cudaGetSymbolAddress, never a device address.
+// Each GPU that loads the library holds its own MEEMB200_STATIC_WS_BYTES copy until the process exits.
+static __device__ __align__(256) unsigned char g_static_ws[MEEMB200_STATIC_WS_BYTES];
+static const int kStaticWsMaxDevices = 64;
+static void* g_static_ws_ptr[kStaticWsMaxDevices];       // device address of g_static_ws per device ordinal, resolved once
+static std::mutex g_static_ws_mu;
+
+// `device` must be the current device of the calling thread (the symbol resolves in the current context).
+static int static_ws_address(int device, void** out) {
+    if (device < 0 || device >= kStaticWsMaxDevices) return fail(MEEMB200_EINVAL, "device ordinal beyond the static-workspace table");
+    std::lock_guard<std::mutex> lock(g_static_ws_mu);
+    if (!g_static_ws_ptr[device]) {
+        int cur = -1;
+        CUDA_TRY(cudaGetDevice(&cur));
+        if (cur != device) return fail(MEEMB200_ECUDA, "static workspace: the plan's device could not be made current");
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_ws));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255) != 0) return fail(MEEMB200_ECUDA, "static workspace: bad symbol address");
+        g_static_ws_ptr[device] = p;
+    }
+    *out = g_static_ws_ptr[device];
+    return MEEMB200_OK;
+}
+
+extern "C" int meemb200_solve_static_ws(meemb200_plan* P, const void* d_in, const MeemOutputs* out, void* stream) {
+    if (!P || !d_in || !out) return fail(MEEMB200_EINVAL, "NULL argument");
+    if (P->info.workspace_bytes > (size_t)MEEMB200_STATIC_WS_BYTES)
+        return fail(MEEMB200_ENOMEM, "plan needs " + std::to_string(P->info.workspace_bytes) + " bytes of workspace, the library's static workspace holds " +
+                                         std::to_string((size_t)MEEMB200_STATIC_WS_BYTES) + " (MEEMB200_STATIC_WS_BYTES): use meemb200_solve with a caller-owned workspace");
+    DeviceGuard guard(P->ctx->device);
+    void* ws = nullptr;
+    int rc = static_ws_address(P->ctx->device, &ws);
+    if (rc) return rc;
+    // Same kernels, same order as meemb200_solve; its prologue zeroes the work-queue counters, the only part of the
+    // workspace that has to start at zero - everything else is written before it is read, whatever the last call left.
+    return meemb200_solve(P, d_in, ws, (size_t)MEEMB200_STATIC_WS_BYTES, out, stream);
 }
 
 extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f,
