@@ -554,6 +554,8 @@ def main():
                 n, t = run_cpu(kind, geoms, omegas, tgt, pool, cores, min_seconds=10.0)
             cpu = {"value": n / t, "unit": UNIT, "cores": cores, "kind": kind,
                    "sample": f"{n} systems sampled evenly from the workload, {cpu_description(kind, cores)}, {t:.1f} s"}
+            from oracle import ref_runner
+            cpu["legs"] = ref_runner.time_legs(geoms, omegas, cores)      # (1) one process, (3) compiled
         details["algo"] = args.algo
         details["geometry_kernel"] = plan.geom_kernel
         line = {"details": details, "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,

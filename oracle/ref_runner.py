@@ -48,6 +48,58 @@ def run_port(g, omegas):
         return mo.run_sweep(og, omegas, g["body_map"], g["modes"])["added_mass"]
 
 
+def run_compiled(g, omegas, nthreads=1):
+    """oracle/meem_cpu.cpp: the reference's dense algorithm compiled (g++ build of the shared closed-form headers, LAPACK
+    zgetrf/zgetrs out of scipy), `nthreads` std::threads over the frequencies.  Returns the added-mass array."""
+    from oracle import meem_cpu
+    return meem_cpu.run_sweep(g["h"], g["a"], g["d"], g["NMK"], g["body_map"], g["modes"], omegas, nthreads=nthreads)["added_mass"]
+
+
+def time_legs(geoms, omegas, cores, budget_s=4.0):
+    """The other CPU legs of BASELINE.md section 4, each on a small bounded sample (~budget_s seconds):
+    (1) the untouched reference in ONE process with the BLAS library's default thread count,
+    (3) the compiled restatement with 1 thread and with `cores` threads (BLAS threads = 1).  systems/s each."""
+    import time
+    legs = {}
+
+    def sample(n_sys):
+        if len(geoms) == 1:
+            idx = np.linspace(0, len(omegas) - 1, min(n_sys, len(omegas))).astype(int)
+            return [(geoms[0], [float(omegas[i]) for i in idx])]
+        ng = max(1, min(len(geoms), n_sys // len(omegas)))
+        return [(g, [float(w) for w in omegas]) for g in geoms[:ng]]
+
+    def timed(fn, n0):
+        n, done, t0 = n0, 0, time.perf_counter()
+        while True:
+            for g, om in sample(n):
+                fn(g, om)
+                done += len(om)
+            el = time.perf_counter() - t0
+            if el >= budget_s or n >= 65536:
+                return done / el, done, el
+            n *= 4
+
+    try:
+        from threadpoolctl import threadpool_info, threadpool_limits
+        blas_threads = max([int(i.get("num_threads", 1)) for i in threadpool_info() if i.get("user_api") == "blas"] or [1])
+    except Exception:
+        threadpool_limits, blas_threads = None, None
+    if reference_available():
+        _load_reference()
+        v, n, t = timed(run_reference, 2)
+        legs["reference_one_process"] = {"value": v, "blas_threads": blas_threads, "sample": f"{n} systems, {t:.1f} s, MEEMEngine.run_and_store_results"}
+    from oracle import meem_cpu
+    if meem_cpu.available():
+        ctx = threadpool_limits(limits=1) if threadpool_limits else contextlib.nullcontext()
+        with ctx:
+            v, n, t = timed(lambda g, om: run_compiled(g, om, 1), 2)
+            legs["compiled_1_thread"] = {"value": v, "sample": f"{n} systems, {t:.1f} s, oracle/meem_cpu.cpp (dense assembly + LAPACK zgetrf/zgetrs, the reference's algorithm)"}
+            v, n, t = timed(lambda g, om: run_compiled(g, om, cores), 2 * cores)
+            legs["compiled_all_cores"] = {"value": v, "threads": cores, "sample": f"{n} systems, {t:.1f} s, same, {cores} threads over the frequencies"}
+    return legs
+
+
 def cpu_chunk(args):
     """Worker of the multiprocessing pool: (kind, geometry dict, omegas) with one BLAS thread per process."""
     kind, g, omegas = args
