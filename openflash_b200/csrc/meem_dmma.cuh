@@ -251,10 +251,10 @@ __host__ __device__ inline void syrk_build_plan(SyrkPlan& plan, int nb) {
     plan.nt = nt;
 }
 
-template <int NI, int NJ>
+template <int NI, int NJ, int KC = kSyrkKC>
 __device__ __forceinline__ void syrk_chunk(const double* As, const double* Bs, int ld, int lc, double (&acc)[4][4][2]) {
 #pragma unroll
-    for (int ks = 0; ks < kSyrkKC / 4; ++ks) {
+    for (int ks = 0; ks < KC / 4; ++ks) {
         double af[NI], bf[NJ];
 #pragma unroll
         for (int i = 0; i < NI; ++i) af[i] = As[(ks * 4 + lc) * ld + i * 8];
@@ -267,10 +267,10 @@ __device__ __forceinline__ void syrk_chunk(const double* As, const double* Bs, i
     }
 }
 // diagonal tile: rows == columns, only blocks j <= i
-template <int NI>
+template <int NI, int KC = kSyrkKC>
 __device__ __forceinline__ void syrk_chunk_diag(const double* As, int ld, int lc, double (&acc)[4][4][2]) {
 #pragma unroll
-    for (int ks = 0; ks < kSyrkKC / 4; ++ks) {
+    for (int ks = 0; ks < KC / 4; ++ks) {
         double af[NI];
 #pragma unroll
         for (int i = 0; i < NI; ++i) af[i] = As[(ks * 4 + lc) * ld + i * 8];
@@ -375,6 +375,265 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
             }
         }
         cp_async_wait<0>();
+        if (has) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (i < nri && j < nci && (a != b || j <= i))
+                        epi((rb0 + i) * 8 + lr, (cb0 + j) * 8 + 2 * lc, acc[i][j][0], acc[i][j][1]);
+        }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Triangular product of the factorised-H form as ONE chunk stream (round 2, v19):
+//   [aug ; W] = LA^T-contraction with B,   aug = the 2R right-hand-side rows (LA columns 0 .. 2R-1, full contraction),
+//   W[m][:] = sum_{k >= m} LA[k][2R + m] B[k][:]   (LA columns 2R .. 2R + Mw - 1: row k of the Cholesky factor L)
+// The output is processed in row groups of 4 8-row blocks (plus one group for the aug rows); group a contracts rows
+// k >= 32 a only.  Per group every warp owns NI x NJ blocks (NJ = nb / 8 column blocks) plus up to 4 "extra" blocks of the
+// nb % 8 left-over column blocks, dealt over the warps block by block, so that all 8 warps (and the 4 SM sub-partitions)
+// carry the same number of DMMAs (nb = 25: 12 or 13 blocks each, against 12 / 16 for an even column split).
+// Operands move in chunks of kTrKC contraction rows: the 32-column LA tile of the group and the WHOLE-width rows of B, one
+// bulk copy (TMA unit) per row, into a ring of `stages` stages with a full (transaction count) and an empty (one arrival
+// per warp) mbarrier per stage.  There is no CTA barrier inside the stream - warps only meet through the ring, so a warp
+// may run up to stages - 2 chunks ahead of the slowest one - and the ring does not drain between groups.
+// Requires N % 8 == 0 (no partial chunk), K even, 8 <= nb <= 32, 2R <= 8.
+constexpr int kTrKC = 8;
+constexpr int kTrLdA = 36;
+constexpr int kTrMaxStages = 8;
+struct TrRing {                                   // static shared memory of the calling kernel
+    uint64_t full[kTrMaxStages], empty[kTrMaxStages];
+};
+__host__ __device__ inline int trmm_stage_doubles(int K) { return kTrKC * (kTrLdA + syrk_lds(K)); }
+__host__ __device__ inline int trmm_stages(int K) {
+    const int s = kGemmSmemDoubles / trmm_stage_doubles(K);
+    return s > kTrMaxStages ? kTrMaxStages : s;
+}
+__host__ __device__ inline bool trmm_fits(int N, int K, int R) {
+    const int nb = (K + 7) >> 3;
+    return (N & 7) == 0 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages(K) >= 4;
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+
+template <int NA, int NJ>
+__device__ __forceinline__ void trmm_chunk(const double* As, const double* Bs, int ldb, int lc, double (&acc)[16][2]) {
+#pragma unroll
+    for (int ks = 0; ks < kTrKC / 4; ++ks) {
+        double af[NA], bf[NJ];
+#pragma unroll
+        for (int i = 0; i < NA; ++i) af[i] = As[(ks * 4 + lc) * kTrLdA + i * 8];
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) bf[j] = Bs[(ks * 4 + lc) * ldb + j * 8];
+#pragma unroll
+        for (int i = 0; i < NA; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) dmma(acc[i * NJ + j][0], acc[i * NJ + j][1], af[i], bf[j]);
+    }
+}
+
+// NJ = nb / 8 column blocks per warp.  bits: per-stage use parity of the ring (bit s), kept by the caller across calls.
+// epi_w(m, n, v0, v1): W row m (0-based), columns n, n + 1;  epi_aug(m, n, v0, v1): aug row m (0 .. 7: check m < 2R)
+template <int NJ, class EpiW, class EpiA>
+__device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __restrict__ B, int R2, int Mw,
+                                int N, int K, double* sm, TrRing& ring, unsigned& bits, EpiW epi_w, EpiA epi_aug) {
+    constexpr int NX = NJ == 4 ? 0 : 4;                           // extra accumulator blocks 4 NJ .. 4 NJ + NX - 1
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int nb = (K + 7) >> 3, ldsb = syrk_lds(K);
+    const int S = trmm_stages(K), stage_doubles = trmm_stage_doubles(K);
+    const int mbw = (Mw + 7) >> 3, ng = (mbw + 3) >> 2;          // W row blocks, row groups
+    const int rem = nb - 8 * NJ;
+    // chunk stream: group -1 (aug) with N / 8 chunks, then groups a = 0 .. ng - 1 with (N - 32 a) / 8 chunks each
+    int total = N / kTrKC;
+    for (int a = 0; a < ng; ++a) total += (N - 32 * a) / kTrKC;
+    const int look = S - 2;                                       // chunks in flight ahead of the consumer
+    // producer state (warp 0): next chunk to issue.  LAT holds the LA tiles of the groups back to back in stream order with
+    // the stage's leading dimension, and B has the stage's leading dimension too, so a chunk is TWO contiguous bulk copies.
+    int pg = -1, pstep = 0, pissued = 0, pst = 0;
+    unsigned pbits = bits;
+    const double* pa = LAT;
+    auto issue = [&]() {
+        if (pissued >= S) mbar_wait(&ring.empty[pst], ((pbits >> pst) & 1u) ^ 1u);   // the stage's previous chunk is consumed
+        const int k0 = (pg < 0 ? 0 : 32 * pg) + kTrKC * pstep;
+        double* As = sm + (long)pst * stage_doubles;
+        double* Bs = As + kTrKC * kTrLdA;
+        if (lane == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&ring.full[pst], (unsigned)(kTrKC * (kTrLdA + ldsb) * sizeof(double)));
+            bulk_g2s(As, pa, (unsigned)(kTrKC * kTrLdA * sizeof(double)), &ring.full[pst]);
+            bulk_g2s(Bs, B + (long)k0 * ldsb, (unsigned)(kTrKC * ldsb * sizeof(double)), &ring.full[pst]);
+        }
+        __syncwarp();
+        pa += kTrKC * kTrLdA;
+        pbits ^= 1u << pst;
+        ++pissued;
+        if (++pst == S) pst = 0;
+        const int gsteps = (N - (pg < 0 ? 0 : 32 * pg)) / kTrKC;
+        if (++pstep == gsteps) { pstep = 0; ++pg; }
+    };
+    asm volatile("fence.proxy.async;" ::: "memory");              // this thread's generic-proxy stores to B (the table) before the bulk reads
+    __syncthreads();                                              // ... everyone's; previous users of the stage memory are done
+    if (warp == 0) for (int i = 0; i < look && pissued < total; ++i) issue();
+    int st = 0;
+    for (int g = -1; g < ng; ++g) {
+        const int NI = g < 0 ? 1 : min(4, mbw - 4 * g);
+        const int gsteps = (N - (g < 0 ? 0 : 32 * g)) / kTrKC;
+        // extra blocks of this warp: e = warp, warp + 8, ... < rem * NI -> (row block e % NI, column block 8 NJ + e / NI)
+        int nx = 0, xi[4], xj[4];
+#pragma unroll
+        for (int x = 0; x < 4; ++x) {
+            const int e = warp + 8 * x;
+            xi[x] = 0; xj[x] = 0;
+            if (e < rem * NI) { xi[x] = e % NI; xj[x] = 8 * NJ + e / NI; nx = x + 1; }
+        }
+        double acc[16][2];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i][0] = acc[i][1] = 0.0;
+        const double* Bw0 = sm + kTrKC * kTrLdA + lr + warp * NJ * 8;
+        for (int step = 0; step < gsteps; ++step) {
+            if (warp == 0 && pissued < total) issue();
+            mbar_wait(&ring.full[st], (bits >> st) & 1u);
+            bits ^= 1u << st;
+            const double* As = sm + (long)st * stage_doubles + lr;
+            const double* Bw = Bw0 + (long)st * stage_doubles;
+            const int na = g < 0 ? 1 : min(NI, step + 1);        // row blocks the chunk's contraction rows reach
+            switch (na) {
+                case 1: trmm_chunk<1, NJ>(As, Bw, ldsb, lc, acc); break;
+                case 2: trmm_chunk<2, NJ>(As, Bw, ldsb, lc, acc); break;
+                case 3: trmm_chunk<3, NJ>(As, Bw, ldsb, lc, acc); break;
+                default: trmm_chunk<4, NJ>(As, Bw, ldsb, lc, acc); break;
+            }
+            if (NX > 0) {
+                const double* Bs = As + kTrKC * kTrLdA;
+#pragma unroll
+                for (int x = 0; x < NX; ++x) {
+                    if (x < nx && xi[x] < na) {                   // warp-uniform
+#pragma unroll
+                        for (int ks = 0; ks < kTrKC / 4; ++ks)
+                            dmma(acc[(4 * NJ + x) & 15][0], acc[(4 * NJ + x) & 15][1],
+                                 As[(ks * 4 + lc) * kTrLdA + xi[x] * 8], Bs[(ks * 4 + lc) * ldsb + xj[x] * 8]);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ring.empty[st]);
+            if (++st == S) st = 0;
+        }
+        // epilogue of the group (no CTA barrier: the stream goes on)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                if (i < NI) {
+                    const int n = (warp * NJ + j) * 8 + 2 * lc;
+                    if (g < 0) epi_aug(lr, n, acc[i * NJ + j][0], acc[i * NJ + j][1]);
+                    else epi_w(32 * g + i * 8 + lr, n, acc[i * NJ + j][0], acc[i * NJ + j][1]);
+                }
+            }
+#pragma unroll
+        for (int x = 0; x < NX; ++x) {
+            if (x < nx) {
+                const int n = xj[x] * 8 + 2 * lc;
+                if (g < 0) epi_aug(lr, n, acc[(4 * NJ + x) & 15][0], acc[(4 * NJ + x) & 15][1]);
+                else epi_w(32 * g + xi[x] * 8 + lr, n, acc[(4 * NJ + x) & 15][0], acc[(4 * NJ + x) & 15][1]);
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Lower triangle of C = W^T W as a chunk stream (round 2, v19): the tile list of cta_syrk_dmma, but the kTrKC-row chunks of W
+// go through the full / empty mbarrier ring of the triangular product - no CTA barrier per chunk, and the ring does not
+// drain between passes (the chunk sequence simply wraps around to W's first rows).  Requires Nc % 8 == 0 (whole 16-byte
+// groups per row) and rows [Kd, pad8(Kd)) of W zero.
+template <int KC>
+__host__ __device__ inline int syrk_stream_stages(int Nc) {
+    const int s = kGemmSmemDoubles / (KC * syrk_lds(Nc));
+    return s > kTrMaxStages ? kTrMaxStages : s;
+}
+template <int KC>
+__host__ __device__ inline bool syrk_stream_fits(int Nc) { return syrk_fits(Nc) && syrk_stream_stages<KC>(Nc) >= 3; }
+
+// W: Kd x Nc row-major with the leading dimension syrk_lds(Nc) of the stages (a chunk is ONE contiguous bulk copy); rows
+// [Kd, pad16(Kd)) must be zero.
+template <int KC, class Epi>
+__device__ void cta_syrk_stream(const double* __restrict__ W, int Nc, int Kd, double* sm, SyrkPlan& plan,
+                                TrRing& ring, unsigned& bits, Epi epi) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int nb = (Nc + 7) >> 3, lds = syrk_lds(Nc);
+    const int ng = (nb + 3) >> 2;
+    const int nchunk = (Kd + KC - 1) / KC;
+    const int S = syrk_stream_stages<KC>(Nc), stage_doubles = KC * lds;
+    asm volatile("fence.proxy.async;" ::: "memory");              // this thread's generic-proxy stores to W before the bulk reads
+    __syncthreads();
+    if (plan.nb != nb) {                         // (re)build the sorted tile list: once per CTA for a uniform batch
+        if (threadIdx.x == 0) syrk_build_plan(plan, nb);
+        __syncthreads();
+        if (threadIdx.x == 0) plan.nb = nb;
+    }
+    const int nt = plan.nt;
+    const int npass = (nt + nwarp - 1) / nwarp;
+    const int total = npass * nchunk;
+    const int look = S > 3 ? S - 2 : S - 1;
+    int pc = 0, pissued = 0, pst = 0;
+    unsigned pbits = bits;
+    auto issue = [&]() {
+        if (pissued >= S) mbar_wait(&ring.empty[pst], ((pbits >> pst) & 1u) ^ 1u);
+        if (lane == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&ring.full[pst], (unsigned)(stage_doubles * sizeof(double)));
+            bulk_g2s(sm + (long)pst * stage_doubles, W + (long)pc * stage_doubles, (unsigned)(stage_doubles * sizeof(double)), &ring.full[pst]);
+        }
+        __syncwarp();
+        pbits ^= 1u << pst;
+        ++pissued;
+        if (++pst == S) pst = 0;
+        if (++pc == nchunk) pc = 0;
+    };
+    if (warp == 0) for (int i = 0; i < look && pissued < total; ++i) issue();
+    int st = 0;
+    for (int t0 = 0; t0 < nt; t0 += nwarp) {
+        const int t = t0 + warp;
+        const bool has = t < nt;
+        const int a = has ? plan.ta[t] : 0, b = has ? plan.tb[t] : 0;
+        const int rb0 = a * nb / ng, rb1 = (a + 1) * nb / ng, cb0 = b * nb / ng, cb1 = (b + 1) * nb / ng;
+        const int nri = rb1 - rb0, nci = cb1 - cb0;
+        const int shape = !has ? -1 : (a == b ? 16 + (nri - 1) : (nri - 1) * 4 + (nci - 1));
+        double acc[4][4][2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int c = 0; c < nchunk; ++c) {
+            if (warp == 0 && pissued < total) issue();
+            mbar_wait(&ring.full[st], (bits >> st) & 1u);
+            bits ^= 1u << st;
+            const double* cur = sm + (long)st * stage_doubles;
+            const double* As = cur + rb0 * 8 + lr;
+            const double* Bs = cur + cb0 * 8 + lr;
+            switch (shape) {
+#define MEEM_SYRK_CASE(NI, NJ) case (NI - 1) * 4 + (NJ - 1): syrk_chunk<NI, NJ, KC>(As, Bs, lds, lc, acc); break;
+                MEEM_SYRK_CASE(1, 1) MEEM_SYRK_CASE(1, 2) MEEM_SYRK_CASE(1, 3) MEEM_SYRK_CASE(1, 4)
+                MEEM_SYRK_CASE(2, 1) MEEM_SYRK_CASE(2, 2) MEEM_SYRK_CASE(2, 3) MEEM_SYRK_CASE(2, 4)
+                MEEM_SYRK_CASE(3, 1) MEEM_SYRK_CASE(3, 2) MEEM_SYRK_CASE(3, 3) MEEM_SYRK_CASE(3, 4)
+                MEEM_SYRK_CASE(4, 1) MEEM_SYRK_CASE(4, 2) MEEM_SYRK_CASE(4, 3) MEEM_SYRK_CASE(4, 4)
+#undef MEEM_SYRK_CASE
+                case 16: syrk_chunk_diag<1, KC>(As, lds, lc, acc); break;
+                case 17: syrk_chunk_diag<2, KC>(As, lds, lc, acc); break;
+                case 18: syrk_chunk_diag<3, KC>(As, lds, lc, acc); break;
+                case 19: syrk_chunk_diag<4, KC>(As, lds, lc, acc); break;
+                default: break;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ring.empty[st]);
+            if (++st == S) st = 0;
+        }
         if (has) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)

@@ -129,8 +129,19 @@ __host__ __device__ inline int64_t gs_base_doubles(int N, int R) {
 // P = Imk^T H Imk - Re D = W^T W - Re D, W = L^T (Pm^T Imk): a triangular product (half the flops of H Imk) followed by
 // a symmetric rank-N update.  hrank <= 0: factorisation not available (H not PSD to rounding, or N too large for the
 // shared-memory factor) and the frequency stage uses H itself.
+// LAT: LA re-tiled for the chunk stream of the triangular product (cta_trmm_stream): tile -1 = columns 0..7 of LA (the
+// aug columns), rows 0..N-1; tile a >= 0 = columns 2R + 32 a .. + 31, rows 32 a .. N-1; every tile row-major with a
+// leading dimension of 36 doubles, so that kTrKC rows of a tile are ONE contiguous bulk copy into the padded stage.
+__host__ __device__ inline int64_t lat_tile_off(int N, int a) {          // doubles, a = -1 .. ng
+    int64_t rows = 0;
+    if (a >= 0) rows = N;
+    for (int i = 0; i < a; ++i) rows += N - 32 * i;
+    return rows * 36;
+}
+__host__ __device__ inline int64_t lat_doubles(int N) { return (N & 7) ? 0 : lat_tile_off(N, (N + 31) / 32); }
+__host__ __device__ inline int64_t gs_lat_off(int N, int R) { return gs_base_doubles(N, R) + (int64_t)N * gs_ldn(N, R) + pad8((N + 1) / 2); }
 __host__ __device__ inline int64_t gs_doubles(int N, int R) {
-    return gs_base_doubles(N, R) + (int64_t)N * gs_ldn(N, R) + pad8((N + 1) / 2);
+    return gs_lat_off(N, R) + lat_doubles(N);
 }
 __host__ __device__ inline size_t hchol_smem_bytes(int N) {
     return chol_smem_bytes(N, 0) + sizeof(double) * (size_t)tri_doubles(N) + sizeof(int) * (size_t)(N + 8);
@@ -885,6 +896,25 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
                 LA[e] = val;
             }
             for (int i = tid; i < N; i += nthr) permg[i] = perm[i];
+            if ((N & 7) == 0) {
+                double* LAT = gs + gs_lat_off(N, R);
+                auto la_val = [&](int k, int c) -> double {
+                    if (c >= ldn) return 0.0;
+                    const int m = c - 2 * R;
+                    if (c < 2 * R) return HT[(int64_t)perm[k] * ldn + N + c];
+                    if (k < rank && m <= k) return (m == k) ? 1.0 / tri[tri_off(k) + k] : tri[tri_off(k) + m];
+                    return 0.0;
+                };
+                const int ngl = (N + 31) / 32;
+                for (int a = -1; a < ngl; ++a) {
+                    const int k0 = a < 0 ? 0 : 32 * a, c0 = a < 0 ? 0 : 2 * R + 32 * a, wc = a < 0 ? 8 : 32;
+                    double* tile = LAT + lat_tile_off(N, a);
+                    for (int e = tid; e < (N - k0) * 36; e += nthr) {
+                        const int kr = e / 36, c = e - kr * 36;
+                        tile[e] = c < wc ? la_val(k0 + kr, c0 + c) : 0.0;
+                    }
+                }
+            }
         }
     }
 }
@@ -1164,7 +1194,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_lu(const void* blob, void* ws, 
 // (rows padded to a multiple of 16 and kept zero beyond the live ones: the bulk-copied contraction chunks of the rank update
 // read whole 16-row chunks)
 __host__ __device__ inline int pad16(int n) { return (n + 15) & ~15; }
-__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * pad16(N) * pad8(K) + 16; }
+__host__ __device__ inline int64_t freq2_slot_doubles(int N, int K, int R) { return 2LL * pad16(N) * syrk_lds(K) + 16; }
 __host__ __device__ inline int64_t freq2_sys_doubles(int K, int R) { return (int64_t)tri_doubles(K) + (int64_t)(3 * R + 2) * pad8(K) + 8; }
 // k_freq_solve dynamic shared memory: Cholesky scratch | xc, vv (X path) | [resident variant: Ptri | aug[R][ldk] | xs[R+1][ldk]]
 __host__ __device__ inline size_t freq2_solve_smem_bytes(int K, int R, int N, bool want_x, bool resident) {
@@ -1193,7 +1223,7 @@ enum { PH_IMK = 0, PH_DOTS, PH_GEMM1, PH_GEMM2, PH_CHOL, PH_BACK, PH_OUT, PH_X, 
 // sines (|theta| eps, theta up to ~1e3); the exact-equality branch |m_k| == lambda is kept.  Row m = 0 and
 // column k = 0 go through the reference-ordered imk().  (meemb200_assemble keeps imk() for every entry.)
 __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* mk, const double* Nk, int N, int K, int ldk,
-                              const int* perm, double* Imk, double* sm, int sm_doubles, int* sh_row0) {
+                              const int* perm, double* Imk, double* sm, int sm_doubles, int* sh_row0, bool batched = false) {
     const int tid = threadIdx.x, nthr = blockDim.x;
 #define HARM(kk) (perm ? perm[kk] : (kk))
     const bool fast = !ex.inf_m0 && (6 * K + 3 * N) <= sm_doubles;
@@ -1247,6 +1277,56 @@ __device__ void cta_imk_table(const Geom& g, const Exterior& ex, const double* m
                 const double lam = tlm[n], sl = tsl[n], cl = tcl[n];
                 const double lsl = lam * sl;
                 double* row = Imk + (long)n * ldk;
+                if (batched) {
+                    // four entries per lane and pass share ONE division: r = 1 / (d0 d1 d2 d3), 1 / d_i = r * (product of the others)
+                    // (prefix products; an entry near a resonance or beyond the row enters the product as 1 and takes the series form)
+                    for (int kp0 = lane_; kp0 < K - 1; kp0 += 128) {
+                        double den[4], num[4];
+                        unsigned nearm = 0;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int kp = kp0 + 32 * i;
+                            const bool valid = kp < K - 1;
+                            const int kc = valid ? kp : kp0;
+                            const double mv = tmk[kc];
+                            const double sp = mv + lam, sd = mv - lam;
+                            num[i] = fma(tpk[kc], cl, -(tqk[kc] * lsl));
+                            const bool nr = fabs(sd * Lh) < 1.0;
+                            den[i] = (nr || !valid) ? 1.0 : sp * sd;
+                            if (nr && valid) nearm |= 1u << i;
+                        }
+                        const double p1 = den[0] * den[1], p2 = p1 * den[2], p3 = p2 * den[3];
+                        double r = 1.0 / p3;
+                        const double i3 = r * p2; r *= den[3];
+                        const double i2 = r * p1; r *= den[2];
+                        const double i1 = r * den[0], i0 = r * den[1];
+                        double val[4] = {num[0] * i0, num[1] * i1, num[2] * i2, num[3] * i3};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int kp = kp0 + 32 * i;
+                            if (nearm & (1u << i)) {
+                                const double mv = tmk[kp];
+                                const double sp = mv + lam, sd = mv - lam;
+                                const double x = sd * Lh, x2 = x * x;
+                                double pl = -8.22063524662432972e-18;
+                                pl = fma(pl, x2, 2.81145725434552076e-15);
+                                pl = fma(pl, x2, -7.64716373181981648e-13);
+                                pl = fma(pl, x2, 1.60590438368216146e-10);
+                                pl = fma(pl, x2, -2.50521083854417188e-08);
+                                pl = fma(pl, x2, 2.75573192239858907e-06);
+                                pl = fma(pl, x2, -1.98412698412698413e-04);
+                                pl = fma(pl, x2, 8.33333333333333333e-03);
+                                pl = fma(pl, x2, -1.66666666666666667e-01);
+                                const double S = fma(x * x2, pl, x);
+                                const double a = tsk[kp] * cl, b = tck[kp] * sl;
+                                val[i] = tnk[kp] * (fma(a + b, sd, S * sp) / (sp * sd));
+                                if (fabs(mv) == lam) val[i] = sqrt(2.0 / Nk[kp + 1]) * Lh / 2.0;
+                            }
+                            if (kp < K - 1) row[kp] = val[i];
+                        }
+                    }
+                    continue;
+                }
                 for (int kp = lane_; kp < K - 1; kp += 32) {
                     const double mv = tmk[kp];
                     const double sp = mv + lam, sd = mv - lam;
@@ -1316,14 +1396,19 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
     __shared__ int sh_item, sh_row0;
     __shared__ SyrkPlan sh_syrk;
     __shared__ __align__(8) uint64_t sh_mbar[kGemmStages];
+    __shared__ __align__(8) TrRing sh_ring;
     unsigned mbar_phase = 0;                               // bit s: parity the next wait on stage s expects
+    unsigned ring_bits = 0;                                // the same for the chunk ring of the triangular product
     if (threadIdx.x == 0) {
         sh_syrk.nb = -1;
         for (int i = 0; i < kGemmStages; ++i) mbar_init(&sh_mbar[i], 1);
+        for (int i = 0; i < kTrMaxStages; ++i) { mbar_init(&sh_ring.full[i], 1); mbar_init(&sh_ring.empty[i], (int)(blockDim.x >> 5)); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     const bool use_bulk = (flags & 4) == 0;
     const bool use_syrk = (flags & 1) == 0;
+    const bool use_stream = (flags & 8) == 0;
+    const bool use_stream_syrk = (flags & 16) == 0;
     DevView v = make_view(blob, ws);
     double* sm = reinterpret_cast<double*>(smem);
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -1345,8 +1430,9 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         __syncthreads();
         const int N = gd.N, K = gd.K, R = gd.R;
         const int ldk = pad8(K), ldn = gs_ldn(N, R);
+        const int lsl = syrk_lds(K);                        // leading dimension of Imk / T in the slot = that of the shared-memory stages
         double* Imk = slot;
-        double* T = Imk + (int64_t)pad16(N) * ldk;
+        double* T = Imk + (int64_t)pad16(N) * lsl;
         double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
         double* P = sys;                                   // packed lower triangle
         double* aug = P + tri_doubles(K);                  // [2R][ldk] right-hand sides r_i, then q_j
@@ -1360,9 +1446,10 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         const bool lmode = hrank > 0;
         const double* LA = gs + gs_base_doubles(N, R);
         const int* perm = reinterpret_cast<const int*>(LA + (int64_t)N * ldn);
+        const double* LAT = gs + gs_lat_off(N, R);
 #define HARM(kk) (lmode ? perm[kk] : (kk))
         // 1. coupling table (columns permuted; rows permuted in the factorised-H form): cta_imk_table
-        cta_imk_table(g, ex, mk, Nk, N, K, ldk, lmode ? perm : nullptr, Imk, sm, kGemmSmemDoubles, &sh_row0);
+        cta_imk_table(g, ex, mk, Nk, N, K, lsl, lmode ? perm : nullptr, Imk, sm, kGemmSmemDoubles, &sh_row0, (flags & 32) == 0);
         for (int kp = tid; kp < K; kp += nthr) {
             const int k = (kp == K - 1) ? 0 : kp + 1;
             const cplx dg = ext_diag(k, g, ex, mk);
@@ -1374,17 +1461,31 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         // sides r_i = -(bc_i Imk[0][:] + Imk^T u_i) (augmented rows of P) and q_j = Imk^T w_j
         // Factorised form: [-r_i ; q_j ; W] = LA^T-contraction with the row-permuted Imk, W = L^T Imk; output rows
         // 2R + m only need contraction rows k >= m (L is lower trapezoidal), which the GEMM skips chunk-wise.
-        if (lmode) {
-            cta_gemm_dmma(LA, ldn, Imk, ldk, 2 * R + hrank, K, N, false, 2 * R, sm, [&](int m, int n, double v0, double v1) {
+        if (lmode && use_stream && trmm_fits(N, K, R)) {
+            // chunk-stream form (meem_dmma.cuh): row groups of W, balanced warp tiles, mbarrier ring without CTA barriers
+            auto epi_w = [&](int m, int n, double v0, double v1) {
+                if (m < hrank && n < K) *reinterpret_cast<double2*>(T + (long)m * lsl + n) = make_double2(v0, v1);
+            };
+            auto epi_a = [&](int m, int n, double v0, double v1) {
+                if (m < 2 * R && n < K) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = m < R ? make_double2(-v0, -v1) : make_double2(v0, v1);
+            };
+            switch (((K + 7) >> 3) >> 3) {
+                case 1: cta_trmm_stream<1>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
+                case 2: cta_trmm_stream<2>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
+                case 3: cta_trmm_stream<3>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
+                default: cta_trmm_stream<4>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
+            }
+        } else if (lmode) {
+            cta_gemm_dmma(LA, ldn, Imk, lsl, 2 * R + hrank, K, N, false, 2 * R, sm, [&](int m, int n, double v0, double v1) {
                 if (n >= K) return;
                 if (m < R) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = make_double2(-v0, -v1);
                 else if (m < 2 * R) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = make_double2(v0, v1);
-                else if (m < 2 * R + hrank) *reinterpret_cast<double2*>(T + (long)(m - 2 * R) * ldk + n) = make_double2(v0, v1);
+                else if (m < 2 * R + hrank) *reinterpret_cast<double2*>(T + (long)(m - 2 * R) * lsl + n) = make_double2(v0, v1);
             });
         } else {
-            cta_gemm_dmma(HT, ldn, Imk, ldk, N + 2 * R, K, N, false, -1, sm, [&](int m, int n, double v0, double v1) {
+            cta_gemm_dmma(HT, ldn, Imk, lsl, N + 2 * R, K, N, false, -1, sm, [&](int m, int n, double v0, double v1) {
                 if (n >= K) return;
-                if (m < N) *reinterpret_cast<double2*>(T + (long)m * ldk + n) = make_double2(v0, v1);
+                if (m < N) *reinterpret_cast<double2*>(T + (long)m * lsl + n) = make_double2(v0, v1);
                 else if (m < N + R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(-v0, -v1);
                 else if (m < N + 2 * R) *reinterpret_cast<double2*>(aug + (long)(m - N) * ldk + n) = make_double2(v0, v1);
             });
@@ -1398,18 +1499,22 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
                 *reinterpret_cast<double2*>(P + tri_off(m) + n) = make_double2(v0, v1);
             }
         };
-        if (lmode && use_syrk && K >= 64 && syrk_fits(K)) {
+        if (lmode && use_syrk && use_stream_syrk && K >= 64 && syrk_stream_fits<16>(K)) {
+            for (int e = tid; e < (pad16(hrank) - hrank) * lsl; e += nthr) T[(int64_t)hrank * lsl + e] = 0.0;
+            if (flags & 64) cta_syrk_stream<8>(T, K, hrank, sm, sh_syrk, sh_ring, ring_bits, store_p);
+            else cta_syrk_stream<16>(T, K, hrank, sm, sh_syrk, sh_ring, ring_bits, store_p);
+        } else if (lmode && use_syrk && K >= 64 && syrk_fits(K)) {
             const bool bulk = use_bulk && (K & 7) == 0;        // whole 64-byte rows: the bulk copies need 16-byte sizes
             if (bulk) {
                 // rows [hrank, pad16(hrank)) of W are read by the last 16-row chunk: zero; then make this CTA's generic-proxy
                 // stores to W visible to the async proxy (TMA reads of global memory)
-                for (int e = tid; e < (pad16(hrank) - hrank) * ldk; e += nthr) T[(int64_t)hrank * ldk + e] = 0.0;
+                for (int e = tid; e < (pad16(hrank) - hrank) * lsl; e += nthr) T[(int64_t)hrank * lsl + e] = 0.0;
                 asm volatile("fence.proxy.async;" ::: "memory");
                 __syncthreads();
             }
-            cta_syrk_dmma(T, ldk, K, hrank, sm, sh_syrk, bulk ? sh_mbar : nullptr, mbar_phase, store_p);
+            cta_syrk_dmma(T, lsl, K, hrank, sm, sh_syrk, bulk ? sh_mbar : nullptr, mbar_phase, store_p);
         }
-        else cta_gemm_dmma(lmode ? T : Imk, ldk, T, ldk, K, K, lmode ? hrank : N, true, -1, sm, store_p);
+        else cta_gemm_dmma(lmode ? T : Imk, lsl, T, lsl, K, K, lmode ? hrank : N, true, -1, sm, store_p);
         PHASE_END(PH_GEMM2);
     }
     if (tid == 0) {
@@ -2379,7 +2484,9 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->max_N = max_N;
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
-    P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0);
+    P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0) |
+                    (getenv("MEEMB200_NO_STREAM") ? 8 : 0) | (getenv("MEEMB200_NO_STREAM_SYRK") ? 16 : 0) |
+                    (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0) | (getenv("MEEMB200_SYRK_KC8") ? 64 : 0);
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
