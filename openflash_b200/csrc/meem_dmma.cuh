@@ -406,23 +406,26 @@ constexpr int kTrMaxStages = 8;
 struct TrRing {                                   // static shared memory of the calling kernel
     uint64_t full[kTrMaxStages], empty[kTrMaxStages];
 };
-__host__ __device__ inline int trmm_stage_doubles(int K) { return kTrKC * (kTrLdA + syrk_lds(K)); }
+template <int KC = kTrKC>
+__host__ __device__ inline int trmm_stage_doubles(int K) { return KC * (kTrLdA + syrk_lds(K)); }
+template <int KC = kTrKC>
 __host__ __device__ inline int trmm_stages(int K) {
-    const int s = kGemmSmemDoubles / trmm_stage_doubles(K);
+    const int s = kGemmSmemDoubles / trmm_stage_doubles<KC>(K);
     return s > kTrMaxStages ? kTrMaxStages : s;
 }
 __host__ __device__ inline bool trmm_fits(int N, int K, int R) {
     const int nb = (K + 7) >> 3;
-    return (N & 7) == 0 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages(K) >= 4;
+    return (N & 7) == 0 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
+// 8 contraction rows (two k-steps) of a warp tile of NA x NJ blocks
 template <int NA, int NJ>
 __device__ __forceinline__ void trmm_chunk(const double* As, const double* Bs, int ldb, int lc, double (&acc)[16][2]) {
 #pragma unroll
-    for (int ks = 0; ks < kTrKC / 4; ++ks) {
+    for (int ks = 0; ks < 2; ++ks) {
         double af[NA], bf[NJ];
 #pragma unroll
         for (int i = 0; i < NA; ++i) af[i] = As[(ks * 4 + lc) * kTrLdA + i * 8];
@@ -435,45 +438,46 @@ __device__ __forceinline__ void trmm_chunk(const double* As, const double* Bs, i
     }
 }
 
-// NJ = nb / 8 column blocks per warp.  bits: per-stage use parity of the ring (bit s), kept by the caller across calls.
+// NJ = nb / 8 column blocks per warp; KC = contraction rows per chunk (8 or 16; the last chunk of a group may hold 8).
+// bits: per-stage use parity of the ring (bit s), kept by the caller across calls.
+// LAT: the LA tiles of the groups back to back in stream order, leading dimension kTrLdA (k_hchol); B: leading dimension
+// syrk_lds(K) = that of the stage - so a chunk is TWO contiguous bulk copies.
 // epi_w(m, n, v0, v1): W row m (0-based), columns n, n + 1;  epi_aug(m, n, v0, v1): aug row m (0 .. 7: check m < 2R)
-template <int NJ, class EpiW, class EpiA>
+template <int NJ, int KC, class EpiW, class EpiA>
 __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __restrict__ B, int R2, int Mw,
                                 int N, int K, double* sm, TrRing& ring, unsigned& bits, EpiW epi_w, EpiA epi_aug) {
     constexpr int NX = NJ == 4 ? 0 : 4;                           // extra accumulator blocks 4 NJ .. 4 NJ + NX - 1
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int lr = lane >> 2, lc = lane & 3;
     const int nb = (K + 7) >> 3, ldsb = syrk_lds(K);
-    const int S = trmm_stages(K), stage_doubles = trmm_stage_doubles(K);
+    const int S = trmm_stages<KC>(K), stage_doubles = trmm_stage_doubles<KC>(K);
     const int mbw = (Mw + 7) >> 3, ng = (mbw + 3) >> 2;          // W row blocks, row groups
     const int rem = nb - 8 * NJ;
-    // chunk stream: group -1 (aug) with N / 8 chunks, then groups a = 0 .. ng - 1 with (N - 32 a) / 8 chunks each
-    int total = N / kTrKC;
-    for (int a = 0; a < ng; ++a) total += (N - 32 * a) / kTrKC;
-    const int look = S - 2;                                       // chunks in flight ahead of the consumer
-    // producer state (warp 0): next chunk to issue.  LAT holds the LA tiles of the groups back to back in stream order with
-    // the stage's leading dimension, and B has the stage's leading dimension too, so a chunk is TWO contiguous bulk copies.
-    int pg = -1, pstep = 0, pissued = 0, pst = 0;
+    // chunk stream: group -1 (aug) over rows 0 .. N-1, then groups a = 0 .. ng - 1 over rows 32 a .. N-1, KC rows per chunk
+    int total = (N + KC - 1) / KC;
+    for (int a = 0; a < ng; ++a) total += (N - 32 * a + KC - 1) / KC;
+    const int look = S > 3 ? S - 2 : S - 1;                       // chunks in flight ahead of the consumer
+    int pg = -1, pk = 0, pissued = 0, pst = 0;                    // producer state (warp 0): next chunk = rows pk .. of group pg
     unsigned pbits = bits;
     const double* pa = LAT;
     auto issue = [&]() {
         if (pissued >= S) mbar_wait(&ring.empty[pst], ((pbits >> pst) & 1u) ^ 1u);   // the stage's previous chunk is consumed
-        const int k0 = (pg < 0 ? 0 : 32 * pg) + kTrKC * pstep;
+        const int rows = min(KC, N - pk);
         double* As = sm + (long)pst * stage_doubles;
-        double* Bs = As + kTrKC * kTrLdA;
+        double* Bs = As + KC * kTrLdA;
         if (lane == 0) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_expect_tx(&ring.full[pst], (unsigned)(kTrKC * (kTrLdA + ldsb) * sizeof(double)));
-            bulk_g2s(As, pa, (unsigned)(kTrKC * kTrLdA * sizeof(double)), &ring.full[pst]);
-            bulk_g2s(Bs, B + (long)k0 * ldsb, (unsigned)(kTrKC * ldsb * sizeof(double)), &ring.full[pst]);
+            mbar_expect_tx(&ring.full[pst], (unsigned)(rows * (kTrLdA + ldsb) * sizeof(double)));
+            bulk_g2s(As, pa, (unsigned)(rows * kTrLdA * sizeof(double)), &ring.full[pst]);
+            bulk_g2s(Bs, B + (long)pk * ldsb, (unsigned)(rows * ldsb * sizeof(double)), &ring.full[pst]);
         }
         __syncwarp();
-        pa += kTrKC * kTrLdA;
+        pa += rows * kTrLdA;
         pbits ^= 1u << pst;
         ++pissued;
         if (++pst == S) pst = 0;
-        const int gsteps = (N - (pg < 0 ? 0 : 32 * pg)) / kTrKC;
-        if (++pstep == gsteps) { pstep = 0; ++pg; }
+        pk += rows;
+        if (pk >= N) { ++pg; pk = 32 * pg; }
     };
     asm volatile("fence.proxy.async;" ::: "memory");              // this thread's generic-proxy stores to B (the table) before the bulk reads
     __syncthreads();                                              // ... everyone's; previous users of the stage memory are done
@@ -481,7 +485,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     int st = 0;
     for (int g = -1; g < ng; ++g) {
         const int NI = g < 0 ? 1 : min(4, mbw - 4 * g);
-        const int gsteps = (N - (g < 0 ? 0 : 32 * g)) / kTrKC;
+        const int k0g = g < 0 ? 0 : 32 * g;
         // extra blocks of this warp: e = warp, warp + 8, ... < rem * NI -> (row block e % NI, column block 8 NJ + e / NI)
         int nx = 0, xi[4], xj[4];
 #pragma unroll
@@ -493,29 +497,33 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
         double acc[16][2];
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i][0] = acc[i][1] = 0.0;
-        const double* Bw0 = sm + kTrKC * kTrLdA + lr + warp * NJ * 8;
-        for (int step = 0; step < gsteps; ++step) {
+        for (int k = k0g; k < N; k += KC) {
             if (warp == 0 && pissued < total) issue();
             mbar_wait(&ring.full[st], (bits >> st) & 1u);
             bits ^= 1u << st;
-            const double* As = sm + (long)st * stage_doubles + lr;
-            const double* Bw = Bw0 + (long)st * stage_doubles;
-            const int na = g < 0 ? 1 : min(NI, step + 1);        // row blocks the chunk's contraction rows reach
-            switch (na) {
-                case 1: trmm_chunk<1, NJ>(As, Bw, ldsb, lc, acc); break;
-                case 2: trmm_chunk<2, NJ>(As, Bw, ldsb, lc, acc); break;
-                case 3: trmm_chunk<3, NJ>(As, Bw, ldsb, lc, acc); break;
-                default: trmm_chunk<4, NJ>(As, Bw, ldsb, lc, acc); break;
-            }
-            if (NX > 0) {
-                const double* Bs = As + kTrKC * kTrLdA;
 #pragma unroll
-                for (int x = 0; x < NX; ++x) {
-                    if (x < nx && xi[x] < na) {                   // warp-uniform
+            for (int h = 0; h < KC / 8; ++h) {
+                if (k + 8 * h < N) {
+                    const double* As = sm + (long)st * stage_doubles + h * 8 * kTrLdA + lr;
+                    const double* Bs = sm + (long)st * stage_doubles + KC * kTrLdA + h * 8 * ldsb + lr;
+                    const double* Bw = Bs + warp * NJ * 8;
+                    const int na = g < 0 ? 1 : min(NI, ((k - k0g) >> 3) + h + 1);   // row blocks these contraction rows reach
+                    switch (na) {
+                        case 1: trmm_chunk<1, NJ>(As, Bw, ldsb, lc, acc); break;
+                        case 2: trmm_chunk<2, NJ>(As, Bw, ldsb, lc, acc); break;
+                        case 3: trmm_chunk<3, NJ>(As, Bw, ldsb, lc, acc); break;
+                        default: trmm_chunk<4, NJ>(As, Bw, ldsb, lc, acc); break;
+                    }
+                    if (NX > 0) {
 #pragma unroll
-                        for (int ks = 0; ks < kTrKC / 4; ++ks)
-                            dmma(acc[(4 * NJ + x) & 15][0], acc[(4 * NJ + x) & 15][1],
-                                 As[(ks * 4 + lc) * kTrLdA + xi[x] * 8], Bs[(ks * 4 + lc) * ldsb + xj[x] * 8]);
+                        for (int x = 0; x < NX; ++x) {
+                            if (x < nx && xi[x] < na) {               // warp-uniform
+#pragma unroll
+                                for (int ks = 0; ks < 2; ++ks)
+                                    dmma(acc[(4 * NJ + x) & 15][0], acc[(4 * NJ + x) & 15][1],
+                                         As[(ks * 4 + lc) * kTrLdA + xi[x] * 8], Bs[(ks * 4 + lc) * ldsb + xj[x] * 8]);
+                            }
+                        }
                     }
                 }
             }

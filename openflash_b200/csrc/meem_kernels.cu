@@ -1432,7 +1432,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         const int ldk = pad8(K), ldn = gs_ldn(N, R);
         const int lsl = syrk_lds(K);                        // leading dimension of Imk / T in the slot = that of the shared-memory stages
         double* Imk = slot;
-        double* T = Imk + (int64_t)pad16(N) * lsl;
+        double* T = Imk + (int64_t)pad16(N) * lsl;             // (re-pointed at Imk below on the chunk-stream path)
         double* sys = v.sysbuf + (int64_t)(item - item0) * v.hdr->sys_stride;
         double* P = sys;                                   // packed lower triangle
         double* aug = P + tri_doubles(K);                  // [2R][ldk] right-hand sides r_i, then q_j
@@ -1462,19 +1462,27 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         // Factorised form: [-r_i ; q_j ; W] = LA^T-contraction with the row-permuted Imk, W = L^T Imk; output rows
         // 2R + m only need contraction rows k >= m (L is lower trapezoidal), which the GEMM skips chunk-wise.
         if (lmode && use_stream && trmm_fits(N, K, R)) {
-            // chunk-stream form (meem_dmma.cuh): row groups of W, balanced warp tiles, mbarrier ring without CTA barriers
+            // chunk-stream form (meem_dmma.cuh): row groups of W, balanced warp tiles, mbarrier ring without CTA barriers.
+            // W overwrites the table IN PLACE: row group a of W replaces rows 32 a .. 32 a + 31 of Imk, which only the groups
+            // <= a contract over and whose bulk reads have all landed before any warp finishes group a - the slot's second
+            // half stays untouched, which halves the L2 footprint of the slots (296 x 353 KB instead of 705 KB at N = K = 200)
+            if ((flags & 256) == 0) T = Imk;
             auto epi_w = [&](int m, int n, double v0, double v1) {
                 if (m < hrank && n < K) *reinterpret_cast<double2*>(T + (long)m * lsl + n) = make_double2(v0, v1);
             };
             auto epi_a = [&](int m, int n, double v0, double v1) {
                 if (m < 2 * R && n < K) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = m < R ? make_double2(-v0, -v1) : make_double2(v0, v1);
             };
+            // 16-row chunks when three stages of them fit (fewer ring hand-overs per DMMA: 3.48 -> 3.38 ms at N = K = 200), else 8
+            const bool kc16 = trmm_stages<16>(K) >= 3 && (flags & 128) == 0;
+#define MEEM_TRMM(NJ_, KC_) cta_trmm_stream<NJ_, KC_>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a)
             switch (((K + 7) >> 3) >> 3) {
-                case 1: cta_trmm_stream<1>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
-                case 2: cta_trmm_stream<2>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
-                case 3: cta_trmm_stream<3>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
-                default: cta_trmm_stream<4>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, epi_w, epi_a); break;
+                case 1: MEEM_TRMM(1, 16); break;
+                case 2: MEEM_TRMM(2, 16); break;
+                case 3: if (kc16) MEEM_TRMM(3, 16); else MEEM_TRMM(3, 8); break;
+                default: MEEM_TRMM(4, 8); break;
             }
+#undef MEEM_TRMM
         } else if (lmode) {
             cta_gemm_dmma(LA, ldn, Imk, lsl, 2 * R + hrank, K, N, false, 2 * R, sm, [&](int m, int n, double v0, double v1) {
                 if (n >= K) return;
@@ -1621,7 +1629,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
         }
         __syncthreads();
         const int64_t sysi = gd.out_sys + f;
-        const int flag_every = flags >> 8;                          // test hook: send every n-th system down the LU re-solve
+        const int flag_every = flags >> 16;                         // test hook: send every n-th system down the LU re-solve
         const int fail = sh_fail | (flag_every > 0 && sysi % flag_every == 0);
         const int status = gstatus | (fail ? 4 : 0);
         if (tid == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
@@ -2486,7 +2494,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0) |
                     (getenv("MEEMB200_NO_STREAM") ? 8 : 0) | (getenv("MEEMB200_NO_STREAM_SYRK") ? 16 : 0) |
-                    (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0) | (getenv("MEEMB200_SYRK_KC8") ? 64 : 0);
+                    (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0) | (getenv("MEEMB200_SYRK_KC8") ? 64 : 0) | (getenv("MEEMB200_TRMM_KC8") ? 128 : 0) | (getenv("MEEMB200_NO_T_ALIAS") ? 256 : 0);
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
@@ -2656,7 +2664,7 @@ extern "C" int meemb200_plan_offsets(const meemb200_plan* p, int32_t g, int64_t 
 // it down the pivoted-LU re-solve (k_freq_lu) - the only way to reach that path with physical inputs.  n = 0 switches it off.
 extern "C" int meemb200_plan_set_test_hook(meemb200_plan* p, int32_t flag_every) {
     if (!p || flag_every < 0 || flag_every >= (1 << 20)) return fail(MEEMB200_EINVAL, "bad argument");
-    p->gemm_flags = (p->gemm_flags & 0xff) | (flag_every << 8);
+    p->gemm_flags = (p->gemm_flags & 0xffff) | (flag_every << 16);
     return MEEMB200_OK;
 }
 extern "C" int meemb200_plan_set_freq(meemb200_plan* p, const double* freq) {
@@ -2738,7 +2746,7 @@ template <int NB> static cudaError_t launch_freq(meemb200_plan* P, const void* i
         const int64_t n_sys = P->info.n_sys;
         const int grid = (int)std::min<int64_t>((n_sys + kSmallWarps - 1) / kSmallWarps, P->solve_grid);
         k_sys_pre<<<(unsigned)((n_sys + 127) / 128), 128, 0, s>>>(in, ws, (int)n_sys);
-        k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters, P->gemm_flags >> 8);
+        k_freq_small<<<grid, 32 * kSmallWarps, smem_small, s>>>(in, ws, o, (int)n_sys, wave_counters, P->gemm_flags >> 16);
         cudaEventRecord(P->ev[3], s);
         cudaEventRecord(P->ev[4], s);
         e = cudaGetLastError();
