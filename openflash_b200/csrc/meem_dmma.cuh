@@ -445,7 +445,7 @@ __device__ __forceinline__ void trmm_chunk(const double* As, const double* Bs, i
 // epi_w(m, n, v0, v1): W row m (0-based), columns n, n + 1;  epi_aug(m, n, v0, v1): aug row m (0 .. 7: check m < 2R)
 template <int NJ, int KC, class EpiW, class EpiA>
 __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __restrict__ B, int R2, int Mw,
-                                int N, int K, double* sm, TrRing& ring, unsigned& bits, EpiW epi_w, EpiA epi_aug) {
+                                int N, int K, double* sm, TrRing& ring, unsigned& bits, int prod_warp, EpiW epi_w, EpiA epi_aug) {
     constexpr int NX = NJ == 4 ? 0 : 4;                           // extra accumulator blocks 4 NJ .. 4 NJ + NX - 1
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int lr = lane >> 2, lc = lane & 3;
@@ -457,6 +457,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     int total = (N + KC - 1) / KC;
     for (int a = 0; a < ng; ++a) total += (N - 32 * a + KC - 1) / KC;
     const int look = S > 3 ? S - 2 : S - 1;                       // chunks in flight ahead of the consumer
+    const int pw = prod_warp < 0 ? (int)(blockDim.x >> 5) - 1 : prod_warp;   // producer: the last warp carries the fewest blocks
     int pg = -1, pk = 0, pissued = 0, pst = 0;                    // producer state (warp 0): next chunk = rows pk .. of group pg
     unsigned pbits = bits;
     const double* pa = LAT;
@@ -481,7 +482,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     };
     asm volatile("fence.proxy.async;" ::: "memory");              // this thread's generic-proxy stores to B (the table) before the bulk reads
     __syncthreads();                                              // ... everyone's; previous users of the stage memory are done
-    if (warp == 0) for (int i = 0; i < look && pissued < total; ++i) issue();
+    if (warp == pw) for (int i = 0; i < look && pissued < total; ++i) issue();
     int st = 0;
     for (int g = -1; g < ng; ++g) {
         const int NI = g < 0 ? 1 : min(4, mbw - 4 * g);
@@ -498,7 +499,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i][0] = acc[i][1] = 0.0;
         for (int k = k0g; k < N; k += KC) {
-            if (warp == 0 && pissued < total) issue();
+            if (warp == pw && pissued < total) issue();
             mbar_wait(&ring.full[st], (bits >> st) & 1u);
             bits ^= 1u << st;
 #pragma unroll
@@ -571,7 +572,7 @@ __host__ __device__ inline bool syrk_stream_fits(int Nc) { return syrk_fits(Nc) 
 // [Kd, pad16(Kd)) must be zero.
 template <int KC, class Epi>
 __device__ void cta_syrk_stream(const double* __restrict__ W, int Nc, int Kd, double* sm, SyrkPlan& plan,
-                                TrRing& ring, unsigned& bits, Epi epi) {
+                                TrRing& ring, unsigned& bits, int prod_warp, Epi epi) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
     const int lr = lane >> 2, lc = lane & 3;
     const int nb = (Nc + 7) >> 3, lds = syrk_lds(Nc);
@@ -589,6 +590,7 @@ __device__ void cta_syrk_stream(const double* __restrict__ W, int Nc, int Kd, do
     const int npass = (nt + nwarp - 1) / nwarp;
     const int total = npass * nchunk;
     const int look = S > 3 ? S - 2 : S - 1;
+    const int pw = prod_warp < 0 ? nwarp - 1 : prod_warp;        // producer: the last warp carries the smallest tiles
     int pc = 0, pissued = 0, pst = 0;
     unsigned pbits = bits;
     auto issue = [&]() {
@@ -604,7 +606,7 @@ __device__ void cta_syrk_stream(const double* __restrict__ W, int Nc, int Kd, do
         if (++pst == S) pst = 0;
         if (++pc == nchunk) pc = 0;
     };
-    if (warp == 0) for (int i = 0; i < look && pissued < total; ++i) issue();
+    if (warp == pw) for (int i = 0; i < look && pissued < total; ++i) issue();
     int st = 0;
     for (int t0 = 0; t0 < nt; t0 += nwarp) {
         const int t = t0 + warp;
@@ -619,7 +621,7 @@ __device__ void cta_syrk_stream(const double* __restrict__ W, int Nc, int Kd, do
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
         for (int c = 0; c < nchunk; ++c) {
-            if (warp == 0 && pissued < total) issue();
+            if (warp == pw && pissued < total) issue();
             mbar_wait(&ring.full[st], (bits >> st) & 1u);
             bits ^= 1u << st;
             const double* cur = sm + (long)st * stage_doubles;
