@@ -1381,7 +1381,7 @@ __global__ void __launch_bounds__(256) k_imk_dump(const void* blob, void* ws, in
     const int N = gd.N, K = gd.K, ldk = pad8(K);
     double* sm = reinterpret_cast<double*>(smem);
     double* Imk = v.slots;                    // scratch: the first slot
-    cta_imk_table(g, ex, mk, Nk, N, K, ldk, nullptr, Imk, sm, 6 * K + 3 * N, &sh_row0);
+    cta_imk_table(g, ex, mk, Nk, N, K, ldk, nullptr, Imk, sm, 6 * K + 3 * N, &sh_row0, true);      // the product's form
     __syncthreads();
     for (int e = threadIdx.x; e < N * K; e += blockDim.x) {
         const int n = e / K, k = e - n * K;

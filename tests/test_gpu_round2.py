@@ -486,3 +486,32 @@ def test_geometry_batch_and_stacked_download(ofb):
     sub = ofb.solve_batch(gb.take([5, 200, 77]), om)
     for k, gi in enumerate([5, 200, 77]):
         assert np.array_equal(sub[k]["added_mass"], ref[gi]["added_mass"])
+
+
+STREAM_OFF = {"MEEMB200_NO_STREAM": "1", "MEEMB200_NO_STREAM_SYRK": "1", "MEEMB200_NO_BATCH_INV": "1"}
+
+
+@pytest.mark.parametrize("modes,heaving", [(64, [0]), (72, [0]), (104, [0, 2]), (128, [1]), (200, [0]), (200, [0, 1, 2]), (224, [0]),
+                                           (248, [0, 1]), (256, [2])])
+def test_chunk_stream_frequency_gemm_vs_classic_path_and_oracle(ofb, monkeypatch, modes, heaving):
+    """k_freq_gemm's chunk-stream form (v19: cta_trmm_stream / cta_syrk_stream, batched inversion in the coupling table)
+    against the tile-by-tile form it replaces (switched back on by the environment) and against the oracle: column-block
+    counts with 0..7 left-over blocks (extra blocks dealt over the warps), 8- and 16-row chunks, 1-3 radiating modes."""
+    h, a, d = 25.0, [10.0, 15.0, 20.0], [20.0, 15.0, 10.0]
+    NMK = [modes] * 4
+    oms = np.linspace(0.2, 2.9, 24)
+    geo = ofb.FlatGeometry.from_body_map(h, a, d, NMK, [0, 1, 2], heaving)
+    new = ofb.BatchPlan([geo], oms)
+    assert "k_freq_gemm" in new.freq_kernel
+    out_new = new.run()[0]
+    for k, v in STREAM_OFF.items():
+        monkeypatch.setenv(k, v)
+    out_old = ofb.BatchPlan([geo], oms).run()[0]
+    for k in STREAM_OFF:
+        monkeypatch.delenv(k)
+    assert np.all(out_new["status"] == 0) and np.all(out_old["status"] == 0)
+    _check(out_new, out_old, tol=1e-12)
+    og = mo.FlatGeometry(h, a, d, NMK)
+    sel = [0, 11, 23]
+    ref = mo.run_sweep(og, [float(oms[i]) for i in sel], [0, 1, 2], heaving)
+    _check({k: out_new[k][sel] for k in ("added_mass", "damping", "excitation_force", "excitation_phase")}, ref)
