@@ -11,7 +11,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libmeemb200.so")
 SOURCES = ["meem_kernels.cu"]
 DEPS = ["meem_kernels.cu", "meem_lu.cuh", "meem_forms.cuh", "meem_math.cuh", "meem_dmma.cuh", "meem_chol.cuh",
-        "meem_geom_coop.cuh", "bessel_coeffs.h",
+        "meem_geom_coop.cuh", "meem_geom_band.cuh", "bessel_coeffs.h",
         os.path.join("..", "..", "include", "meemb200.h")]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -138,10 +138,10 @@ __host__ __device__ inline int64_t lat_tile_off(int N, int a) {          // doub
     for (int i = 0; i < a; ++i) rows += N - 32 * i;
     return rows * 36;
 }
-__host__ __device__ inline int64_t lat_doubles(int N) { return (N & 7) ? 0 : lat_tile_off(N, (N + 31) / 32); }
+__host__ __device__ inline int64_t lat_doubles(int N, int K, int R) { return trmm_fits(N, K, R) ? lat_tile_off(N, (N + 31) / 32) : 0; }   // only where the chunk stream runs
 __host__ __device__ inline int64_t gs_lat_off(int N, int R) { return gs_base_doubles(N, R) + (int64_t)N * gs_ldn(N, R) + pad8((N + 1) / 2); }
-__host__ __device__ inline int64_t gs_doubles(int N, int R) {
-    return gs_lat_off(N, R) + lat_doubles(N);
+__host__ __device__ inline int64_t gs_doubles(int N, int R, int K) {
+    return gs_lat_off(N, R) + lat_doubles(N, K, R);
 }
 __host__ __device__ inline size_t hchol_smem_bytes(int N) {
     return chol_smem_bytes(N, 0) + sizeof(double) * (size_t)tri_doubles(N) + sizeof(int) * (size_t)(N + 8);
@@ -896,7 +896,7 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
                 LA[e] = val;
             }
             for (int i = tid; i < N; i += nthr) permg[i] = perm[i];
-            if ((N & 7) == 0) {
+            if (trmm_fits(N, gd.K, R)) {
                 double* LAT = gs + gs_lat_off(N, R);
                 auto la_val = [&](int k, int c) -> double {
                     if (c >= ldn) return 0.0;
@@ -2432,7 +2432,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
         if (ins.second) { RootSet rs; rs.h = h; rs.K = L.K; rs.pad = 0; rs.off = 0; sets.push_back(rs); }
         gd.root_set = ins.first->second;
         gd.tab_off = tab_tot; tab_tot += table_doubles(L);
-        gd.gs_off = gs_tot; gs_tot += gs_doubles(gd.N, R);
+        gd.gs_off = gs_tot; gs_tot += gs_doubles(gd.N, R, gd.K);
         if (b->want_x && schur) { gd.xg_off = xg_tot; xg_tot += (int64_t)gd.p * (gd.N + R); }
         else gd.xg_off = -1;
         gd.out_rr = n_rr; n_rr += (int64_t)F * R * R;
