@@ -1466,7 +1466,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
             // W overwrites the table IN PLACE: row group a of W replaces rows 32 a .. 32 a + 31 of Imk, which only the groups
             // <= a contract over and whose bulk reads have all landed before any warp finishes group a - the slot's second
             // half stays untouched, which halves the L2 footprint of the slots (296 x 353 KB instead of 705 KB at N = K = 200)
-            if ((flags & 256) == 0) T = Imk;
+            T = Imk;
             auto epi_w = [&](int m, int n, double v0, double v1) {
                 if (m < hrank && n < K) *reinterpret_cast<double2*>(T + (long)m * lsl + n) = make_double2(v0, v1);
             };
@@ -1474,8 +1474,8 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
                 if (m < 2 * R && n < K) *reinterpret_cast<double2*>(aug + (long)m * ldk + n) = m < R ? make_double2(-v0, -v1) : make_double2(v0, v1);
             };
             // 16-row chunks when three stages of them fit (fewer ring hand-overs per DMMA: 3.48 -> 3.38 ms at N = K = 200), else 8
-            const bool kc16 = trmm_stages<16>(K) >= 3 && (flags & 128) == 0;
-#define MEEM_TRMM(NJ_, KC_) cta_trmm_stream<NJ_, KC_>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, (flags & 512) ? 0 : -1, epi_w, epi_a)
+            const bool kc16 = trmm_stages<16>(K) >= 3;
+#define MEEM_TRMM(NJ_, KC_) cta_trmm_stream<NJ_, KC_>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, -1, epi_w, epi_a)
             switch (((K + 7) >> 3) >> 3) {
                 case 1: MEEM_TRMM(1, 16); break;
                 case 2: MEEM_TRMM(2, 16); break;
@@ -1509,8 +1509,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
         };
         if (lmode && use_syrk && use_stream_syrk && K >= 64 && syrk_stream_fits<16>(K)) {
             for (int e = tid; e < (pad16(hrank) - hrank) * lsl; e += nthr) T[(int64_t)hrank * lsl + e] = 0.0;
-            if (flags & 64) cta_syrk_stream<8>(T, K, hrank, sm, sh_syrk, sh_ring, ring_bits, (flags & 512) ? 0 : -1, store_p);
-            else cta_syrk_stream<16>(T, K, hrank, sm, sh_syrk, sh_ring, ring_bits, (flags & 512) ? 0 : -1, store_p);
+            cta_syrk_stream<16>(T, K, hrank, sm, sh_syrk, sh_ring, ring_bits, -1, store_p);
         } else if (lmode && use_syrk && K >= 64 && syrk_fits(K)) {
             const bool bulk = use_bulk && (K & 7) == 0;        // whole 64-byte rows: the bulk copies need 16-byte sizes
             if (bulk) {
@@ -2494,7 +2493,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
     P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0) |
                     (getenv("MEEMB200_NO_STREAM") ? 8 : 0) | (getenv("MEEMB200_NO_STREAM_SYRK") ? 16 : 0) |
-                    (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0) | (getenv("MEEMB200_SYRK_KC8") ? 64 : 0) | (getenv("MEEMB200_TRMM_KC8") ? 128 : 0) | (getenv("MEEMB200_NO_T_ALIAS") ? 256 : 0) | (getenv("MEEMB200_PROD_WARP0") ? 512 : 0);
+                    (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0);
     P->use_small = b->algo == MEEMB200_ALGO_SCHUR && max_K <= kSmallMax && max_N <= kSmallMax && max_R <= kSmallMaxR && !b->want_x &&
                    !getenv("MEEMB200_NO_SMALL");
     const bool fits = P->smem_chol + 2048 <= limit;
