@@ -45,3 +45,8 @@ p = ofb.BatchPlan([tri], om)
 p.set_test_hook(2)
 print("hook", p.run()[0]["status"], flush=True)
 print("imk", p.imk_table(0, 0).shape, "coef", p.coefficients(np.ones(tri.size, dtype=complex), 0, 0).shape, flush=True)
+# chunk-stream k_freq_gemm (v19): 72 modes -> 9 column blocks (one extra block per pass), 104 -> 13 (five extras), 16- and 8-row chunks
+for nm in (72, 104):
+    big = ofb.FlatGeometry.from_body_map(25.0, [10.0, 15.0, 20.0], [20.0, 15.0, 10.0], [nm] * 4, [0, 1, 2], [0, 2])
+    run(f"tri {nm} modes chunk stream", [big])
+    run(f"tri {nm} modes classic gemm", [big], {"MEEMB200_NO_STREAM": "1", "MEEMB200_NO_STREAM_SYRK": "1", "MEEMB200_NO_BATCH_INV": "1"})
