@@ -399,7 +399,7 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
 // bulk copy (TMA unit) per row, into a ring of `stages` stages with a full (transaction count) and an empty (one arrival
 // per warp) mbarrier per stage.  There is no CTA barrier inside the stream - warps only meet through the ring, so a warp
 // may run up to stages - 2 chunks ahead of the slowest one - and the ring does not drain between groups.
-// Requires N % 8 == 0 (no partial chunk), K even, 8 <= nb <= 32, 2R <= 8.
+// Requires K even, 8 <= nb <= 32, 2R <= 8, N >= 32; LAT and B zero-padded to a multiple of 8 rows.
 constexpr int kTrKC = 8;
 constexpr int kTrLdA = 36;
 constexpr int kTrMaxStages = 8;
@@ -415,7 +415,7 @@ __host__ __device__ inline int trmm_stages(int K) {
 }
 __host__ __device__ inline bool trmm_fits(int N, int K, int R) {
     const int nb = (K + 7) >> 3;
-    return (N & 7) == 0 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
+    return N >= 32 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
@@ -454,6 +454,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     const int mbw = (Mw + 7) >> 3, ng = (mbw + 3) >> 2;          // W row blocks, row groups
     const int rem = nb - 8 * NJ;
     // chunk stream: group -1 (aug) over rows 0 .. N-1, then groups a = 0 .. ng - 1 over rows 32 a .. N-1, KC rows per chunk
+    const int Np = (N + 7) & ~7;                                  // LAT tiles and B are zero-padded to whole 8-row chunks
     int total = (N + KC - 1) / KC;
     for (int a = 0; a < ng; ++a) total += (N - 32 * a + KC - 1) / KC;
     const int look = S > 3 ? S - 2 : S - 1;                       // chunks in flight ahead of the consumer
@@ -463,7 +464,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     const double* pa = LAT;
     auto issue = [&]() {
         if (pissued >= S) mbar_wait(&ring.empty[pst], ((pbits >> pst) & 1u) ^ 1u);   // the stage's previous chunk is consumed
-        const int rows = min(KC, N - pk);
+        const int rows = min(KC, Np - pk);
         double* As = sm + (long)pst * stage_doubles;
         double* Bs = As + KC * kTrLdA;
         if (lane == 0) {
@@ -478,7 +479,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
         ++pissued;
         if (++pst == S) pst = 0;
         pk += rows;
-        if (pk >= N) { ++pg; pk = 32 * pg; }
+        if (pk >= Np) { ++pg; pk = 32 * pg; }
     };
     asm volatile("fence.proxy.async;" ::: "memory");              // this thread's generic-proxy stores to B (the table) before the bulk reads
     __syncthreads();                                              // ... everyone's; previous users of the stage memory are done

@@ -132,10 +132,11 @@ __host__ __device__ inline int64_t gs_base_doubles(int N, int R) {
 // LAT: LA re-tiled for the chunk stream of the triangular product (cta_trmm_stream): tile -1 = columns 0..7 of LA (the
 // aug columns), rows 0..N-1; tile a >= 0 = columns 2R + 32 a .. + 31, rows 32 a .. N-1; every tile row-major with a
 // leading dimension of 36 doubles, so that kTrKC rows of a tile are ONE contiguous bulk copy into the padded stage.
-__host__ __device__ inline int64_t lat_tile_off(int N, int a) {          // doubles, a = -1 .. ng
+__host__ __device__ inline int64_t lat_tile_off(int N, int a) {          // doubles, a = -1 .. ng; rows zero-padded to pad8(N)
+    const int Np = pad8(N);
     int64_t rows = 0;
-    if (a >= 0) rows = N;
-    for (int i = 0; i < a; ++i) rows += N - 32 * i;
+    if (a >= 0) rows = Np;
+    for (int i = 0; i < a; ++i) rows += Np - 32 * i;
     return rows * 36;
 }
 __host__ __device__ inline int64_t lat_doubles(int N, int K, int R) { return trmm_fits(N, K, R) ? lat_tile_off(N, (N + 31) / 32) : 0; }   // only where the chunk stream runs
@@ -899,7 +900,7 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
             if (trmm_fits(N, gd.K, R)) {
                 double* LAT = gs + gs_lat_off(N, R);
                 auto la_val = [&](int k, int c) -> double {
-                    if (c >= ldn) return 0.0;
+                    if (c >= ldn || k >= N) return 0.0;
                     const int m = c - 2 * R;
                     if (c < 2 * R) return HT[(int64_t)perm[k] * ldn + N + c];
                     if (k < rank && m <= k) return (m == k) ? 1.0 / tri[tri_off(k) + k] : tri[tri_off(k) + m];
@@ -909,7 +910,7 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
                 for (int a = -1; a < ngl; ++a) {
                     const int k0 = a < 0 ? 0 : 32 * a, c0 = a < 0 ? 0 : 2 * R + 32 * a, wc = a < 0 ? 8 : 32;
                     double* tile = LAT + lat_tile_off(N, a);
-                    for (int e = tid; e < (N - k0) * 36; e += nthr) {
+                    for (int e = tid; e < (pad8(N) - k0) * 36; e += nthr) {
                         const int kr = e / 36, c = e - kr * 36;
                         tile[e] = c < wc ? la_val(k0 + kr, c0 + c) : 0.0;
                     }
@@ -1450,6 +1451,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
 #define HARM(kk) (lmode ? perm[kk] : (kk))
         // 1. coupling table (columns permuted; rows permuted in the factorised-H form): cta_imk_table
         cta_imk_table(g, ex, mk, Nk, N, K, lsl, lmode ? perm : nullptr, Imk, sm, kGemmSmemDoubles, &sh_row0, (flags & 32) == 0);
+        for (int e = tid; e < (pad8(N) - N) * lsl; e += nthr) Imk[(int64_t)N * lsl + e] = 0.0;      // the chunk stream reads whole 8-row chunks
         for (int kp = tid; kp < K; kp += nthr) {
             const int k = (kp == K - 1) ? 0 : kp + 1;
             const cplx dg = ext_diag(k, g, ex, mk);
