@@ -516,3 +516,19 @@ def test_chunk_stream_frequency_gemm_vs_classic_path_and_oracle(ofb, monkeypatch
     sel = [0, 11, 23]
     ref = mo.run_sweep(og, [float(oms[i]) for i in sel], [0, 1, 2], heaving)
     _check({k: out_new[k][sel] for k in ("added_mass", "damping", "excitation_force", "excitation_phase")}, ref)
+
+
+def test_chunk_stream_heterogeneous_batch_ring_state(ofb):
+    """One plan whose systems alternate between mode counts with different ring geometries (16- and 8-row chunks, 3 to 6 stages,
+    with and without extra blocks) and the classic path (60 modes: fewer than 8 column blocks): the persistent CTAs carry the
+    ring's per-stage parity bits from one system to the next, so every geometry must come out exactly as when solved alone."""
+    h, a, d = 25.0, [10.0, 15.0, 20.0], [20.0, 15.0, 10.0]
+    oms = np.linspace(0.25, 2.75, 40)
+    modes = [200, 72, 248, 60, 104, 150, 232, 90]
+    geos = [ofb.FlatGeometry.from_body_map(h, a, d, [m] * 4, [0, 1, 2], [0]) for m in modes]
+    together = ofb.BatchPlan(geos, oms).run()
+    for m, geo, got in zip(modes, geos, together):
+        alone = ofb.BatchPlan([geo], oms).run()[0]
+        assert np.all(got["status"] == 0), m
+        for k in ("added_mass", "damping", "excitation_force", "excitation_phase"):
+            assert np.array_equal(got[k], alone[k]), (m, k, float(np.max(np.abs(got[k] - alone[k]))))
