@@ -2329,6 +2329,9 @@ struct meemb200_plan {
     int64_t max_FK;
     cudaEvent_t ev[6];      // 0 start, 1 after roots, 2 after geometry, 3 after last k_freq_gemm, 4 after last k_freq_solve, 5 end
     bool ev_ok;
+    cudaStream_t side = nullptr;       // roots run here, concurrently with the geometry stage (meemb200_solve; created at its first call)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool no_side = false;              // MEEMB200_NO_ROOTS_OVERLAP
     char* host_call_base;   // device allocation of meemb200_solve_host (the one call that owns device memory), kept for the next call
     size_t host_call_bytes;
 };
@@ -2493,6 +2496,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
     P->max_N = max_N;
     P->smem_hchol = std::min<size_t>(hchol_smem_bytes(max_N), limit - 1024);
     if (getenv("MEEMB200_NO_HCHOL")) P->smem_hchol = 0;          // tuning / test override: frequency stage uses H itself
+    P->no_side = getenv("MEEMB200_NO_ROOTS_OVERLAP") != nullptr;
     P->gemm_flags = (getenv("MEEMB200_NO_SYRK") ? 1 : 0) | (getenv("MEEMB200_NO_LL") ? 2 : 0) | (getenv("MEEMB200_NO_BULK") ? 4 : 0) |
                     (getenv("MEEMB200_NO_STREAM") ? 8 : 0) | (getenv("MEEMB200_NO_STREAM_SYRK") ? 16 : 0) |
                     (getenv("MEEMB200_NO_BATCH_INV") ? 32 : 0);
@@ -2644,6 +2648,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
 
 extern "C" int meemb200_plan_destroy(meemb200_plan* p) {
     if (p && p->ev_ok) for (auto& e : p->ev) cudaEventDestroy(e);
+    if (p && p->side) { cudaStreamDestroy(p->side); cudaEventDestroy(p->ev_fork); cudaEventDestroy(p->ev_join); }
     if (p && p->host_call_base) { DeviceGuard guard(p->ctx->device); cudaFree(p->host_call_base); }
     delete p;
     return MEEMB200_OK;
@@ -2794,19 +2799,24 @@ template <int NB> static cudaError_t launch_dense(meemb200_plan* P, const void* 
     return cudaGetLastError();
 }
 
-static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cudaStream_t s) {
+static int enqueue_prologue(meemb200_plan* P, const void* d_in, void* d_ws, cudaStream_t s, cudaStream_t sr = nullptr) {
     const BlobHeader* h = P->hdr();
+    if (!sr) sr = s;                                       // sr: the stream of the wavenumber kernels
     CUDA_TRY(cudaMemsetAsync(static_cast<char*>(d_ws) + h->ws_counters, 0, 256 + 8 * (size_t)P->n_waves, s));
     const int nt = h->n_sets * h->n_freq;
-    k_m0<<<(nt + 127) / 128, 128, 0, s>>>(d_in, d_ws);
+    k_m0<<<(nt + 127) / 128, 128, 0, sr>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
     dim3 grid((unsigned)((P->max_FK + 127) / 128), (unsigned)std::min(h->n_sets, 65535));
-    k_mk<<<grid, 128, 0, s>>>(d_in, d_ws);
+    k_mk<<<grid, 128, 0, sr>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
     return MEEMB200_OK;
 }
 
-extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, const MeemOutputs* out, void* stream) {
+// side_ok: the wavenumber kernels (k_m0, k_mk) may run on the plan's side stream, forked from and joined back into `stream`
+// with events (graph-capture safe), concurrently with the radial tables and the geometry stage, which do not read the roots -
+// big_tricylinder: 0.07 ms of roots hidden behind k_geom_coop2 / k_hchol.  meemb200_solve_static_ws passes false: its
+// contract is to create nothing but the six timing events.
+static int solve_impl(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, const MeemOutputs* out, void* stream, bool side_ok) {
     if (!P || !d_in || !d_ws || !out) return fail(MEEMB200_EINVAL, "NULL argument");
     if (ws_bytes < P->info.workspace_bytes) return fail(MEEMB200_ENOMEM, "workspace too small");
     if (!out->added_mass || !out->damping || !out->exc_force || !out->exc_phase || !out->m0 || !out->status)
@@ -2821,8 +2831,19 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
     }
     OutPtrs o{out->added_mass, out->damping, out->exc_force, out->exc_phase, out->m0, out->status, h->want_x ? out->x : nullptr};
     CUDA_TRY(cudaEventRecord(P->ev[0], s));
-    int rc = enqueue_prologue(P, d_in, d_ws, s);
+    const bool side = side_ok && !P->no_side;
+    if (side && !P->side) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&P->side, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&P->ev_fork, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&P->ev_join, cudaEventDisableTiming));
+    }
+    if (side) {     // the fork event follows every earlier reader of the roots on `stream` (the previous solve's frequency stage)
+        CUDA_TRY(cudaEventRecord(P->ev_fork, s));
+        CUDA_TRY(cudaStreamWaitEvent(P->side, P->ev_fork, 0));
+    }
+    int rc = enqueue_prologue(P, d_in, d_ws, s, side ? P->side : s);
     if (rc) return rc;
+    if (side) CUDA_TRY(cudaEventRecord(P->ev_join, P->side));
     CUDA_TRY(cudaEventRecord(P->ev[1], s));
     k_tables<<<h->n_geom, 128, 0, s>>>(d_in, d_ws);
     CUDA_TRY(cudaGetLastError());
@@ -2838,15 +2859,20 @@ extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, si
             k_hchol<<<std::min(h->n_geom, 8 * P->ctx->sm_count), hthreads, std::max<size_t>(P->smem_hchol, 1024), s>>>(d_in, d_ws, (unsigned)P->smem_hchol);
             CUDA_TRY(cudaGetLastError());
         }
+        if (side) CUDA_TRY(cudaStreamWaitEvent(s, P->ev_join, 0));
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
         CUDA_TRY(P->nb_freq == 8 ? launch_freq<8>(P, d_in, d_ws, o, s) : P->nb_freq == 4 ? launch_freq<4>(P, d_in, d_ws, o, s) : launch_freq<2>(P, d_in, d_ws, o, s));
     } else {
+        if (side) CUDA_TRY(cudaStreamWaitEvent(s, P->ev_join, 0));
         CUDA_TRY(cudaEventRecord(P->ev[2], s));
         CUDA_TRY(P->nb_dense == 8 ? launch_dense<8>(P, d_in, d_ws, o, s) : P->nb_dense == 4 ? launch_dense<4>(P, d_in, d_ws, o, s) : launch_dense<2>(P, d_in, d_ws, o, s));
     }
     if (h->algo != MEEMB200_ALGO_SCHUR) { CUDA_TRY(cudaEventRecord(P->ev[3], s)); CUDA_TRY(cudaEventRecord(P->ev[4], s)); }
     CUDA_TRY(cudaEventRecord(P->ev[5], s));
     return MEEMB200_OK;
+}
+extern "C" int meemb200_solve(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, const MeemOutputs* out, void* stream) {
+    return solve_impl(P, d_in, d_ws, ws_bytes, out, stream, true);
 }
 
 extern "C" int meemb200_last_timing(meemb200_plan* P, float ms[5]) {
@@ -2985,7 +3011,7 @@ extern "C" int meemb200_solve_static_ws(meemb200_plan* P, const void* d_in, cons
     if (rc) return rc;
     // Same kernels, same order as meemb200_solve; its prologue zeroes the work-queue counters, the only part of the
     // workspace that has to start at zero - everything else is written before it is read, whatever the last call left.
-    return meemb200_solve(P, d_in, ws, (size_t)MEEMB200_STATIC_WS_BYTES, out, stream);
+    return solve_impl(P, d_in, ws, (size_t)MEEMB200_STATIC_WS_BYTES, out, stream, false);
 }
 
 extern "C" int meemb200_assemble(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_bytes, int32_t g, int32_t f,
