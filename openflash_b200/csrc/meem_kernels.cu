@@ -849,7 +849,8 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
         // largest diagonal entry
         double dmax = -INFINITY;
         bool nan = false;
-        for (int i = tid; i < N; i += nthr) { const double x = HT[(int64_t)i * ldn + i]; dmax = fmax(dmax, x); nan |= !(x == x); }
+        double* diagv = sm;                                // the diagonal, staged for thread 0's serial scan (the factorisation's scratch is free until then)
+        for (int i = tid; i < N; i += nthr) { const double x = HT[(int64_t)i * ldn + i]; diagv[i] = x; dmax = fmax(dmax, x); nan |= !(x == x); }
         if (nan) dmax = INFINITY;
         for (int o = 16; o; o >>= 1) dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
         if (lane == 0) red_v[warp] = dmax;
@@ -861,22 +862,25 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
         if (tid == 0) {
             int nz = 0, bad = !(dmax > 0.0) || !(dmax < INFINITY);
             for (int i = 0; i < N && !bad; ++i) {
-                const double x = HT[(int64_t)i * ldn + i];
+                const double x = diagv[i];
                 if (x > tol) perm[nz++] = i;
                 else if (x < -tol) bad = 1;
             }
             if (!bad) {
                 int z = nz;
-                for (int i = 0; i < N; ++i) if (!(HT[(int64_t)i * ldn + i] > tol)) perm[z++] = i;
+                for (int i = 0; i < N; ++i) if (!(diagv[i] > tol)) perm[z++] = i;
             }
             sh_rank = bad ? -1 : nz;
         }
         __syncthreads();
         int rank = sh_rank;
         if (rank > 0) {
-            for (int e = tid; e < rank * rank; e += nthr) {
-                const int r = e / rank, c = e - r * rank;
-                if (c <= r) tri[tri_off(r) + c] = HT[(int64_t)perm[r] * ldn + perm[c]];
+            __syncthreads();                                   // thread 0 is done with diagv (it aliases the scratch, not tri)
+            for (int r = warp; r < rank; r += nwarp) {         // one row per warp, lanes over the columns: no index division, and
+                const double* src = HT + (int64_t)perm[r] * ldn;   // perm is the identity up to the zero rows moved to the end
+                double* dst = tri + tri_off(r);
+#pragma unroll 4
+                for (int c = lane; c <= r; c += 32) dst[c] = src[perm[c]];
             }
             TriMat P;
             P.p = tri; P.aug = tri; P.K = rank; P.lda = 0;
