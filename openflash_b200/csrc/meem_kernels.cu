@@ -875,12 +875,18 @@ __global__ void __launch_bounds__(kHcholThreads) k_hchol(const void* blob, void*
         __syncthreads();
         int rank = sh_rank;
         if (rank > 0) {
-            __syncthreads();                                   // thread 0 is done with diagv (it aliases the scratch, not tri)
-            for (int r = warp; r < rank; r += nwarp) {         // one row per warp, lanes over the columns: no index division, and
-                const double* src = HT + (int64_t)perm[r] * ldn;   // perm is the identity up to the zero rows moved to the end
-                double* dst = tri + tri_off(r);
+            if (rank >= 64) {
+                for (int r = warp; r < rank; r += nwarp) {     // one row per warp, lanes over the columns: no index division, and
+                    const double* src = HT + (int64_t)perm[r] * ldn;   // perm is the identity up to the zero rows moved to the end
+                    double* dst = tri + tri_off(r);
 #pragma unroll 4
-                for (int c = lane; c <= r; c += 32) dst[c] = src[perm[c]];
+                    for (int c = lane; c <= r; c += 32) dst[c] = src[perm[c]];
+                }
+            } else {                                           // small blocks (design sweeps, N = 16): rows shorter than a warp
+                for (int e = tid; e < rank * rank; e += nthr) {
+                    const int r = e / rank, c = e - r * rank;
+                    if (c <= r) tri[tri_off(r) + c] = HT[(int64_t)perm[r] * ldn + perm[c]];
+                }
             }
             TriMat P;
             P.p = tri; P.aug = tri; P.K = rank; P.lda = 0;
