@@ -395,12 +395,15 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
 // k >= 32 a only.  Per group every warp owns NI x NJ blocks (NJ = nb / 8 column blocks) plus up to 4 "extra" blocks of the
 // nb % 8 left-over column blocks, dealt over the warps block by block, so that all 8 warps (and the 4 SM sub-partitions)
 // carry the same number of DMMAs (nb = 25: 12 or 13 blocks each, against 12 / 16 for an even column split).
-// Operands move in chunks of kTrKC contraction rows: the 32-column LA tile of the group and the WHOLE-width rows of B, one
-// bulk copy (TMA unit) per row, into a ring of `stages` stages with a full (transaction count) and an empty (one arrival
-// per warp) mbarrier per stage.  There is no CTA barrier inside the stream - warps only meet through the ring, so a warp
-// may run up to stages - 2 chunks ahead of the slowest one - and the ring does not drain between groups.
+// Operands move in chunks of KC (16, or 8 when three 16-row stages do not fit) contraction rows: the 32-column LA tile of the
+// group and the WHOLE-width rows of B.  Both sources are laid out with the leading dimensions of the stage (LAT: the tiles
+// re-packed by k_hchol with 36-double rows; B: syrk_lds(K)), so a chunk is TWO contiguous bulk copies (TMA unit) issued by one
+// lane of the producer warp - per-row copies (16 UBLKCP per chunk, serialised in one warp) starved the consumers.  The ring
+// has a full (transaction count) and an empty (one arrival per warp) mbarrier per stage; there is no CTA barrier inside the
+// stream - warps only meet through the ring - and the ring does not drain between groups.  The producer is the CTA's LAST
+// warp, which carries the fewest blocks.
 // Requires K even, 8 <= nb <= 32, 2R <= 8, N >= 32; LAT and B zero-padded to a multiple of 8 rows.
-constexpr int kTrKC = 8;
+constexpr int kTrKC = 8;                          // smallest chunk (the granularity of LAT's zero padding and of the triangular skip)
 constexpr int kTrLdA = 36;
 constexpr int kTrMaxStages = 8;
 struct TrRing {                                   // static shared memory of the calling kernel
@@ -444,7 +447,7 @@ __device__ __forceinline__ void trmm_chunk(const double* As, const double* Bs, i
 // syrk_lds(K) = that of the stage - so a chunk is TWO contiguous bulk copies.
 // epi_w(m, n, v0, v1): W row m (0-based), columns n, n + 1;  epi_aug(m, n, v0, v1): aug row m (0 .. 7: check m < 2R)
 template <int NJ, int KC, class EpiW, class EpiA>
-__device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __restrict__ B, int R2, int Mw,
+__device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __restrict__ B, int Mw,
                                 int N, int K, double* sm, TrRing& ring, unsigned& bits, int prod_warp, EpiW epi_w, EpiA epi_aug) {
     constexpr int NX = NJ == 4 ? 0 : 4;                           // extra accumulator blocks 4 NJ .. 4 NJ + NX - 1
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

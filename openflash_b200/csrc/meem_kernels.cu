@@ -1487,7 +1487,7 @@ __global__ void __launch_bounds__(256, 2) k_freq_gemm(const void* blob, void* ws
             };
             // 16-row chunks when three stages of them fit (fewer ring hand-overs per DMMA: 3.48 -> 3.38 ms at N = K = 200), else 8
             const bool kc16 = trmm_stages<16>(K) >= 3;
-#define MEEM_TRMM(NJ_, KC_) cta_trmm_stream<NJ_, KC_>(LAT, Imk, 2 * R, hrank, N, K, sm, sh_ring, ring_bits, -1, epi_w, epi_a)
+#define MEEM_TRMM(NJ_, KC_) cta_trmm_stream<NJ_, KC_>(LAT, Imk, hrank, N, K, sm, sh_ring, ring_bits, -1, epi_w, epi_a)
             switch (((K + 7) >> 3) >> 3) {
                 case 1: MEEM_TRMM(1, 16); break;
                 case 2: MEEM_TRMM(2, 16); break;
