@@ -220,7 +220,12 @@ int meemb200_plan_set_test_hook(meemb200_plan* plan, int32_t flag_every);
  * kind 0: out[r] = offset (doubles) of row r of the packed lower-triangular system matrix for r = 0..n, out[n+1] = padded
  *         size of the K = n triangle;
  * kind 1: warp-tile list of the symmetric rank update for n columns: out[0] = tiles, then per tile
- *         (group a, group b, first row block, row blocks, first column block, column blocks), largest tile first. */
+ *         (group a, group b, first row block, row blocks, first column block, column blocks), largest tile first.
+ * kind 2: chunk stream of the triangular product of k_freq_gemm for N = K = n (one zero row of H): out[0..7] = applies (0/1),
+ *         rows per chunk, ring stages, row groups, chunks of the whole stream, column blocks, doubles of the re-tiled factor,
+ *         leading dimension of the table in the slot; then per row group 0..7 ten ints: row blocks, first row, and the number
+ *         of 8x8 blocks each of the 8 warps owns;
+ * kind 3: offsets (doubles) of the re-tiled factor's tiles -1 (aug columns), 0 .. (n+31)/32 (out[last] = its size). */
 int meemb200_debug_layout(int kind, int n, int* out, int out_len);
 
 #ifdef __cplusplus

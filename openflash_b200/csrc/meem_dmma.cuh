@@ -420,6 +420,20 @@ __host__ __device__ inline bool trmm_fits(int N, int K, int R) {
     const int nb = (K + 7) >> 3;
     return N >= 32 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
 }
+// Blocks of one row group (NI row blocks) that warp `warp` of 8 owns: NI x (nb / 8) plus its share of the (nb % 8) NI extra
+// blocks, dealt block by block (extra e -> warp e % 8).  Host-visible through meemb200_debug_layout (CPU tests).
+__host__ __device__ inline int trmm_warp_extras(int nb, int NI, int warp) {
+    const int ext = (nb & 7) * NI;
+    return warp < ext ? (ext - warp + 7) / 8 : 0;
+}
+__host__ __device__ inline int trmm_warp_blocks(int nb, int NI, int warp) { return NI * (nb >> 3) + trmm_warp_extras(nb, NI, warp); }
+// Chunks of the whole stream: the aug group over rows 0 .. N-1, then group a over rows 32 a .. N-1, KC rows per chunk.
+__host__ __device__ inline int trmm_total_chunks(int N, int Mw, int KC) {
+    const int ng = (((Mw + 7) >> 3) + 3) >> 2;
+    int total = (N + KC - 1) / KC;
+    for (int a = 0; a < ng; ++a) total += (N - 32 * a + KC - 1) / KC;
+    return total;
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
@@ -458,8 +472,7 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
     const int rem = nb - 8 * NJ;
     // chunk stream: group -1 (aug) over rows 0 .. N-1, then groups a = 0 .. ng - 1 over rows 32 a .. N-1, KC rows per chunk
     const int Np = (N + 7) & ~7;                                  // LAT tiles and B are zero-padded to whole 8-row chunks
-    int total = (N + KC - 1) / KC;
-    for (int a = 0; a < ng; ++a) total += (N - 32 * a + KC - 1) / KC;
+    const int total = trmm_total_chunks(N, Mw, KC);
     const int look = S > 3 ? S - 2 : S - 1;                       // chunks in flight ahead of the consumer
     const int pw = prod_warp < 0 ? (int)(blockDim.x >> 5) - 1 : prod_warp;   // producer: the last warp carries the fewest blocks
     int pg = -1, pk = 0, pissued = 0, pst = 0;                    // producer state (warp 0): next chunk = rows pk .. of group pg
@@ -492,12 +505,13 @@ __device__ void cta_trmm_stream(const double* __restrict__ LAT, const double* __
         const int NI = g < 0 ? 1 : min(4, mbw - 4 * g);
         const int k0g = g < 0 ? 0 : 32 * g;
         // extra blocks of this warp: e = warp, warp + 8, ... < rem * NI -> (row block e % NI, column block 8 NJ + e / NI)
-        int nx = 0, xi[4], xj[4];
+        const int nx = trmm_warp_extras(nb, NI, warp);
+        int xi[4], xj[4];
 #pragma unroll
         for (int x = 0; x < 4; ++x) {
             const int e = warp + 8 * x;
             xi[x] = 0; xj[x] = 0;
-            if (e < rem * NI) { xi[x] = e % NI; xj[x] = 8 * NJ + e / NI; nx = x + 1; }
+            if (e < rem * NI) { xi[x] = e % NI; xj[x] = 8 * NJ + e / NI; }
         }
         double acc[16][2];
 #pragma unroll

@@ -2924,6 +2924,27 @@ extern "C" int meemb200_debug_layout(int kind, int n, int* out, int out_len) {
         }
         return MEEMB200_OK;
     }
+    if (kind == 2) {      // chunk stream of the triangular product for N = K = n, Mw = n - 1 (one zero row of H)
+        if (out_len < 8 + 8 * 10) return fail(MEEMB200_EINVAL, "output too short");
+        const int nb = (n + 7) >> 3, Mw = n - 1, mbw = (Mw + 7) >> 3, ngr = (mbw + 3) >> 2;
+        const bool fits = trmm_fits(n, n, 1);
+        const int kc = (nb >> 3) >= 4 ? 8 : (nb >> 3) == 3 ? (trmm_stages<16>(n) >= 3 ? 16 : 8) : 16;
+        out[0] = fits; out[1] = kc; out[2] = kc == 16 ? trmm_stages<16>(n) : trmm_stages<8>(n); out[3] = ngr;
+        out[4] = fits ? trmm_total_chunks(n, Mw, kc) : 0; out[5] = nb; out[6] = (int)(lat_doubles(n, n, 1)); out[7] = syrk_lds(n);
+        for (int a = 0; a < 8; ++a) {     // per group: NI, first row, blocks of the 8 warps
+            int* o = out + 8 + 10 * a;
+            const int NI = a < ngr ? std::min(4, mbw - 4 * a) : 0;
+            o[0] = NI; o[1] = 32 * a;
+            for (int w = 0; w < 8; ++w) o[2 + w] = NI ? trmm_warp_blocks(nb, NI, w) : 0;
+        }
+        return MEEMB200_OK;
+    }
+    if (kind == 3) {      // LAT (the factor re-tiled for the stream): tile offsets in doubles for N = n, tiles -1 .. (n + 31) / 32
+        const int nt = (n + 31) / 32;
+        if (out_len < nt + 2) return fail(MEEMB200_EINVAL, "output too short");
+        for (int a = -1; a <= nt; ++a) out[a + 1] = (int)lat_tile_off(n, a);
+        return MEEMB200_OK;
+    }
     return fail(MEEMB200_EINVAL, "unknown kind");
 }
 

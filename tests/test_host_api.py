@@ -153,6 +153,46 @@ def test_packed_triangle_and_syrk_tile_layouts():
     assert lib.meemb200_debug_layout(1, 1000, buf, len(buf)) != 0          # too wide for the staged SYRK: refused, not garbage
 
 
+def test_chunk_stream_layouts_of_the_frequency_gemm():
+    """Host view of the chunk stream of k_freq_gemm's triangular product (meemb200_debug_layout kinds 2 and 3; integer
+    functions only, no GPU): every row group's blocks are dealt to the 8 warps exactly once and within one block of each
+    other, a warp never holds more than 16 accumulator blocks, the ring has at least 3 stages of whatever chunk size is
+    chosen, the chunk count matches the row groups, and the re-tiled factor's tiles are back to back with 36-double rows."""
+    lib = _lib.load()
+    lib.meemb200_debug_layout.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    out = (ctypes.c_int * 88)()
+    seen_kc = set()
+    for n in (56, 64, 72, 90, 100, 104, 128, 150, 184, 200, 224, 232, 248, 256, 264, 400):
+        assert lib.meemb200_debug_layout(2, n, out, 88) == 0
+        fits, kc, stages, ngr, chunks, nb, lat, lds = out[0:8]
+        assert nb == (n + 7) // 8
+        assert fits == int(8 <= nb <= 32 and n % 2 == 0), n            # the stream's range: 8 .. 32 column blocks, even K
+        assert lds % 16 == 4 and lds >= nb * 8 + 4                      # slot rows: conflict-free fragment loads, room for every block
+        if not fits:
+            assert lat == 0                                             # no re-tiled factor where the classic path runs
+            continue
+        seen_kc.add(kc)
+        assert kc in (8, 16) and stages >= 3 and stages * kc * (36 + lds) <= 12800
+        mbw = (n - 1 + 7) // 8
+        assert ngr == (mbw + 3) // 4
+        assert chunks == -(-n // kc) + sum(-(-(n - 32 * a) // kc) for a in range(ngr))
+        for a in range(ngr):
+            NI, row0, *blocks = out[8 + 10 * a: 18 + 10 * a]
+            assert NI == min(4, mbw - 4 * a) and row0 == 32 * a
+            assert sum(blocks) == NI * nb                               # every block of the group exactly once
+            assert max(blocks) - min(blocks) <= 1 and max(blocks) <= 16  # balanced over the warps, fits the accumulators
+            assert blocks == sorted(blocks, reverse=True)               # the last warp (the producer) is the lightest
+        np8 = (n + 7) // 8 * 8
+        assert lat == 36 * (np8 + sum(np8 - 32 * a for a in range((n + 31) // 32)))
+        nt = (n + 31) // 32
+        tiles = (ctypes.c_int * (nt + 2))()
+        assert lib.meemb200_debug_layout(3, n, tiles, nt + 2) == 0
+        off = list(tiles)
+        assert off[0] == 0 and off[1] == 36 * np8 and off[-1] == lat
+        assert all(off[a + 2] - off[a + 1] == 36 * (np8 - 32 * a) for a in range(nt))
+    assert seen_kc == {8, 16}
+
+
 def test_results_netcdf_export_roundtrip(tmp_path):
     """Results.export_to_netcdf (results.py:252-269): variable names, dimensions and the real / imag split survive a round
     trip through the NetCDF file (scipy reader; xarray-free image)."""
