@@ -532,3 +532,23 @@ def test_chunk_stream_heterogeneous_batch_ring_state(ofb):
         assert np.all(got["status"] == 0), m
         for k in ("added_mass", "damping", "excitation_force", "excitation_phase"):
             assert np.array_equal(got[k], alone[k]), (m, k, float(np.max(np.abs(got[k] - alone[k]))))
+
+
+@pytest.mark.parametrize("NMK", [[64, 48, 40, 96], [30, 72, 100, 64], [90, 90, 200, 104]])
+def test_chunk_stream_unequal_mode_counts(ofb, monkeypatch, NMK):
+    """N (modes of the last interior region) != K (exterior modes): the stream's row groups follow N and rank(H), its column
+    blocks and ring follow K - against the classic path (1e-12) and the oracle (1e-10)."""
+    h, a, d = 25.0, [10.0, 15.0, 20.0], [20.0, 15.0, 10.0]
+    oms = np.linspace(0.3, 2.6, 12)
+    geo = ofb.FlatGeometry.from_body_map(h, a, d, NMK, [0, 1, 2], [0, 2])
+    out_new = ofb.BatchPlan([geo], oms).run()[0]
+    for k, v in STREAM_OFF.items():
+        monkeypatch.setenv(k, v)
+    out_old = ofb.BatchPlan([geo], oms).run()[0]
+    for k in STREAM_OFF:
+        monkeypatch.delenv(k)
+    assert np.all(out_new["status"] == 0) and np.all(out_old["status"] == 0)
+    _check(out_new, out_old, tol=1e-12)
+    sel = [0, 6, 11]
+    ref = mo.run_sweep(mo.FlatGeometry(h, a, d, NMK), [float(oms[i]) for i in sel], [0, 1, 2], [0, 2])
+    _check({k: out_new[k][sel] for k in ("added_mass", "damping", "excitation_force", "excitation_phase")}, ref)
