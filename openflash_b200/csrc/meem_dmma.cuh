@@ -402,7 +402,8 @@ __device__ void cta_syrk_dmma(const double* __restrict__ W, int ldw, int Nc, int
 // has a full (transaction count) and an empty (one arrival per warp) mbarrier per stage; there is no CTA barrier inside the
 // stream - warps only meet through the ring - and the ring does not drain between groups.  The producer is the CTA's LAST
 // warp, which carries the fewest blocks.
-// Requires K even, 8 <= nb <= 32, 2R <= 8, N >= 32; LAT and B zero-padded to a multiple of 8 rows.
+// Requires 8 <= nb <= 32, 2R <= 8, N >= 32; LAT and B zero-padded to a multiple of 8 rows.  Columns K .. 8 nb - 1 of B may hold
+// anything (finite or not): they only feed output columns that are never stored or, for odd K, the one pad column next to K - 1.
 constexpr int kTrKC = 8;                          // smallest chunk (the granularity of LAT's zero padding and of the triangular skip)
 constexpr int kTrLdA = 36;
 constexpr int kTrMaxStages = 8;
@@ -418,7 +419,7 @@ __host__ __device__ inline int trmm_stages(int K) {
 }
 __host__ __device__ inline bool trmm_fits(int N, int K, int R) {
     const int nb = (K + 7) >> 3;
-    return N >= 32 && (K & 1) == 0 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
+    return N >= 32 && nb >= 8 && nb <= 32 && 2 * R <= 8 && trmm_stages<kTrKC>(K) >= 4;
 }
 // Blocks of one row group (NI row blocks) that warp `warp` of 8 owns: NI x (nb / 8) plus its share of the (nb % 8) NI extra
 // blocks, dealt block by block (extra e -> warp e % 8).  Host-visible through meemb200_debug_layout (CPU tests).

@@ -491,13 +491,13 @@ def test_geometry_batch_and_stacked_download(ofb):
 STREAM_OFF = {"MEEMB200_NO_STREAM": "1", "MEEMB200_NO_STREAM_SYRK": "1", "MEEMB200_NO_BATCH_INV": "1"}
 
 
-@pytest.mark.parametrize("modes,heaving", [(64, [0]), (72, [0]), (90, [2]), (100, [0]), (104, [0, 2]), (128, [1]), (150, [0, 1]), (200, [0]),
+@pytest.mark.parametrize("modes,heaving", [(64, [0]), (72, [0]), (75, [0, 1]), (90, [2]), (99, [1]), (100, [0]), (104, [0, 2]), (128, [1]), (150, [0, 1]), (200, [0]),
                                            (200, [0, 1, 2]), (224, [0]), (248, [0, 1]), (256, [2])])
 def test_chunk_stream_frequency_gemm_vs_classic_path_and_oracle(ofb, monkeypatch, modes, heaving):
     """k_freq_gemm's chunk-stream form (v19: cta_trmm_stream / cta_syrk_stream, batched inversion in the coupling table)
     against the tile-by-tile form it replaces (switched back on by the environment) and against the oracle: column-block
     counts with 0..7 left-over blocks (extra blocks dealt over the warps), 8- and 16-row chunks, mode counts that are not a
-    multiple of 8 (zero-padded last chunk), 1-3 radiating modes."""
+    multiple of 8 (zero-padded last chunk), odd mode counts (the pad column next to K - 1), 1-3 radiating modes."""
     h, a, d = 25.0, [10.0, 15.0, 20.0], [20.0, 15.0, 10.0]
     NMK = [modes] * 4
     oms = np.linspace(0.2, 2.9, 24)
