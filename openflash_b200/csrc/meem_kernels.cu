@@ -1641,8 +1641,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_freq_solve(const void* blob, 
         __syncthreads();
         const int64_t sysi = gd.out_sys + f;
         const int flag_every = flags >> 16;                         // test hook: send every n-th system down the LU re-solve
+        // a system whose geometry stage already failed (overflow: NaN by the reference's convention too) is NOT sent to the
+        // pivoted-LU re-solve: its outputs are NaN whatever that would compute (C5: 8 such systems of 400 modes cost 10 ms there)
         const int fail = sh_fail | (flag_every > 0 && sysi % flag_every == 0);
-        const int status = gstatus | (fail ? 4 : 0);
+        const int status = gstatus | ((fail && !gstatus) ? 4 : 0);
         if (tid == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
         const double ze = linv_last * linv_last;
         const double den = 1.0 + beta * beta * ze * ze;
@@ -1967,7 +1969,8 @@ __global__ void __launch_bounds__(32 * kSmallWarps, 6) k_freq_small(const void* 
         __syncwarp();
         // 6. coefficients (same closure as k_freq_solve)
         const int64_t sysi = gd.out_sys + f;
-        const int status = gstatus | ((S.fail || (flag_every > 0 && sysi % flag_every == 0)) ? 4 : 0);
+        const bool hook = flag_every > 0 && sysi % flag_every == 0;
+        const int status = gstatus | (((S.fail || hook) && !gstatus) ? 4 : 0);
         if (lane == 0) { out.m0[sysi] = m0; out.status[sysi] = status; }
         const double linv_last = S.Li[(K - 1) * kCholLdP + K - 1];
         const double beta = S.beta;
