@@ -2300,6 +2300,8 @@ struct meemb200_ctx {
     int device;
     int sm_count;
     size_t smem_optin;
+    cudaStream_t side = nullptr;       // one side stream per context (created at the first solve that uses it), shared by its plans:
+    std::mutex side_mu;                // a stream per plan made every one-problem call of the class API pay a stream creation
 };
 // Launches go to the context's device whatever the caller's current device is; the caller's choice is restored.
 struct DeviceGuard {
@@ -2342,7 +2344,7 @@ struct meemb200_plan {
     int64_t max_FK;
     cudaEvent_t ev[6];      // 0 start, 1 after roots, 2 after geometry, 3 after last k_freq_gemm, 4 after last k_freq_solve, 5 end
     bool ev_ok;
-    cudaStream_t side = nullptr;       // roots run here, concurrently with the geometry stage (meemb200_solve; created at its first call)
+    cudaStream_t side = nullptr;       // the context's side stream: roots run there, concurrently with the geometry stage (meemb200_solve)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool no_side = false;              // MEEMB200_NO_ROOTS_OVERLAP
     char* host_call_base;   // device allocation of meemb200_solve_host (the one call that owns device memory), kept for the next call
@@ -2368,7 +2370,11 @@ extern "C" int meemb200_create(int device, meemb200_ctx** out) {
     *out = c;
     return MEEMB200_OK;
 }
-extern "C" int meemb200_destroy(meemb200_ctx* c) { delete c; return MEEMB200_OK; }
+extern "C" int meemb200_destroy(meemb200_ctx* c) {
+    if (c && c->side) { DeviceGuard guard(c->device); cudaStreamDestroy(c->side); }
+    delete c;
+    return MEEMB200_OK;
+}
 extern "C" int meemb200_sm_count(const meemb200_ctx* c) { return c ? c->sm_count : MEEMB200_EINVAL; }
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -2661,7 +2667,7 @@ extern "C" int meemb200_plan_create(meemb200_ctx* ctx, const MeemBatch* b, meemb
 
 extern "C" int meemb200_plan_destroy(meemb200_plan* p) {
     if (p && p->ev_ok) for (auto& e : p->ev) cudaEventDestroy(e);
-    if (p && p->side) { cudaStreamDestroy(p->side); cudaEventDestroy(p->ev_fork); cudaEventDestroy(p->ev_join); }
+    if (p && p->ev_fork) { cudaEventDestroy(p->ev_fork); cudaEventDestroy(p->ev_join); }
     if (p && p->host_call_base) { DeviceGuard guard(p->ctx->device); cudaFree(p->host_call_base); }
     delete p;
     return MEEMB200_OK;
@@ -2846,7 +2852,11 @@ static int solve_impl(meemb200_plan* P, const void* d_in, void* d_ws, size_t ws_
     CUDA_TRY(cudaEventRecord(P->ev[0], s));
     const bool side = side_ok && !P->no_side;
     if (side && !P->side) {
-        CUDA_TRY(cudaStreamCreateWithFlags(&P->side, cudaStreamNonBlocking));
+        {
+            std::lock_guard<std::mutex> lk(P->ctx->side_mu);
+            if (!P->ctx->side) CUDA_TRY(cudaStreamCreateWithFlags(&P->ctx->side, cudaStreamNonBlocking));
+        }
+        P->side = P->ctx->side;
         CUDA_TRY(cudaEventCreateWithFlags(&P->ev_fork, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&P->ev_join, cudaEventDisableTiming));
     }
